@@ -1,0 +1,131 @@
+"""CPU tests that pin the oracle: the C restatement against the golden vectors the reference produced,
+and (where the compiled reference is present) against the reference itself on fresh inputs."""
+import numpy as np
+import pytest
+
+from tests.cases import CASES, build_case, input_checksums, load_synthetic, rel_l2
+
+
+def _run_restatement(res, case):
+    """The frame loop of the reference's main() (source/main.cpp:131-140) around the restatement."""
+    H, frames = case["H"], case["frames"]
+    kw = dict(case["kw"])
+    sums = res.ray_sums(H, kw.get("nranks", 1))
+    xs, sts, its = [], [], []
+    guess = case["x0"]
+    for f in range(frames.shape[0]):
+        x, st, it = res.solve(H, frames[f], x0=guess, lap=case["lap"], sums=sums, **kw)
+        xs.append(x)
+        sts.append(st)
+        its.append(it)
+        guess = None if case["no_guess"] else x
+    return np.stack(xs), np.array(sts), np.array(its)
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_restatement_matches_golden(name, restatement, golden):
+    case = build_case(name, restatement)
+    # the regenerated inputs are the ones the reference saw
+    np.testing.assert_array_equal(input_checksums(case), golden[name + "/checksums"])
+    x, st, it = _run_restatement(restatement, case)
+    np.testing.assert_array_equal(st, golden[name + "/status"])
+    np.testing.assert_array_equal(it, golden[name + "/iterations"])
+    # same additions in the same order -> equal to the last bit for the linear solver; libm pow/exp/log of the
+    # log solver are the same library calls, so those agree too, but leave one ulp of slack there
+    if CASES[name]["kw"].get("logarithmic"):
+        assert rel_l2(x, golden[name + "/x"]) < 1e-14
+    else:
+        np.testing.assert_array_equal(x, golden[name + "/x"])
+
+
+def test_golden_covers_both_status_codes(golden):
+    sts = np.concatenate([golden[n + "/status"] for n in CASES])
+    assert set(sts.tolist()) == {0, -1}
+
+
+@pytest.mark.parametrize("kw", [
+    dict(),
+    dict(nranks=2),
+    dict(nranks=5, lap=True, beta_laplace=5e-2),
+    dict(logarithmic=True, lap=True, relaxation=0.5, nranks=2),
+])
+def test_restatement_matches_live_reference(kw, restatement, reference):
+    syn = load_synthetic()
+    P, V = 257, 93
+    H = restatement.fill_synthetic(P, V, 1234)
+    g = restatement.forward(H, syn.emission_profile(V))
+    g[5] = -1.0
+    kw = dict(kw)
+    lap = syn.laplacian_coo(V) if kw.pop("lap", False) else None
+    xr, sr, ir = reference.solve(H, g, lap=lap, max_iterations=60, conv_tolerance=1e-6, **kw)
+    xo, so, io = restatement.solve(H, g, lap=lap, max_iterations=60, conv_tolerance=1e-6, **kw)
+    assert (sr, ir) == (so, io)
+    assert rel_l2(xo, xr) < 1e-14
+
+
+def test_reference_rank_count_invariance(restatement, reference):
+    """1 vs N thread-ranks of the unmodified reference agree to rounding (different summation split only)."""
+    syn = load_synthetic()
+    H = restatement.fill_synthetic(200, 64, 77)
+    g = restatement.forward(H, syn.emission_profile(64))
+    x1, s1, i1 = reference.solve(H, g, max_iterations=40, conv_tolerance=1e-30)
+    for n in (2, 3, 8):
+        xn, sn, inn = reference.solve(H, g, max_iterations=40, conv_tolerance=1e-30, nranks=n)
+        assert (sn, inn) == (s1, i1)
+        assert rel_l2(xn, x1) < 1e-12
+
+
+def test_gpu_semantics_switch_only_matters_for_masked_guess(restatement):
+    """The two deviations of the reference GPU path: negative g clipped in the initial
+    guess, and the 1e-7*max(g) floor on the starting solution."""
+    syn = load_synthetic()
+    H = restatement.fill_synthetic(192, 80, 8)
+    g = restatement.forward(H, syn.emission_profile(80))
+    a = restatement.solve(H, g, max_iterations=20, conv_tolerance=1e-30)[0]
+    b = restatement.solve(H, g, max_iterations=20, conv_tolerance=1e-30, gpu_semantics=True)[0]
+    assert rel_l2(b, a) < 1e-6  # all g >= 0, x0 far above the floor -> same path up to the floor
+    g2 = g.copy()
+    g2[::7] = -1.0
+    a = restatement.solve(H, g2, max_iterations=2, conv_tolerance=1e-30)[0]
+    b = restatement.solve(H, g2, max_iterations=2, conv_tolerance=1e-30, gpu_semantics=True)[0]
+    assert rel_l2(b, a) > 1e-4  # the initial guesses differ
+
+
+def test_shard_range_is_the_reference_partition(restatement):
+    # source/main.cpp:67-68
+    for npixel, n in ((10, 3), (8192, 2), (200000, 8), (7, 7), (1000003, 8)):
+        ranges = [restatement.shard_range(npixel, n, r) for r in range(n)]
+        assert ranges[0][0] == 0
+        for r in range(n):
+            off, cnt = ranges[r]
+            assert off == r * (npixel // n) + min(r, npixel % n)
+            assert cnt == npixel // n + (1 if r < npixel % n else 0)
+            if r:
+                assert off == ranges[r - 1][0] + ranges[r - 1][1]
+        assert ranges[-1][0] + ranges[-1][1] == npixel
+
+
+def test_generator_scale_and_shard_invariance(restatement):
+    V = 4096
+    H = restatement.fill_synthetic(64, V, 42)
+    assert H.min() > 0
+    assert 0.5 < H.sum(axis=1).mean() < 1.5  # physical scale: ray lengths of order one
+    # every element is an integer < 2^24 times one power of two
+    q = H.astype(np.float64) * 2.0 ** restatement.lib.oracle_synth_exponent(V)
+    assert np.all(q == np.round(q)) and q.max() < 2 ** 24
+    # rows generated in a later block are the same rows
+    tail = restatement.fill_synthetic(16, V, 42, row0=48)
+    np.testing.assert_array_equal(tail, H[48:])
+
+
+def test_laplacian_helper_convention():
+    syn = load_synthetic()
+    V = 12 * 15
+    idx, val = syn.laplacian_coo(V)
+    assert idx.dtype == np.uint64 and val.dtype == np.float32
+    assert np.all(np.diff(idx.astype(np.int64)) > 0)  # sorted, no duplicates
+    L = np.zeros((V, V))
+    L[(idx // V).astype(int), (idx % V).astype(int)] = val
+    np.testing.assert_array_equal(L, L.T)
+    np.testing.assert_array_equal(L.sum(axis=1), 0)  # constants are in the null space
+    assert L.diagonal().min() == 2 and L.diagonal().max() == 4
