@@ -1,0 +1,175 @@
+/* sart_b200.h -- C ABI of libsart_b200.so: a B200 (sm_100a) constrained-SART engine that is a drop-in for the
+ * solver path of vsnever/mpi-cuda-sartsolver (SARTSolverMPICuda / LogSARTSolverMPICuda).
+ *
+ * One process drives one GPU and owns one row shard of the ray-transfer matrix, exactly like one MPI rank of the
+ * reference (source/main.cpp:63-104). Plain pointers and sizes only: no C++ or torch types cross this boundary, no
+ * exceptions, no exit(). Every function returns SART_OK (0) or an error code; the text is in sart_last_error()
+ * (thread-local). File:line citations name the reference interface each entry point replaces
+ * (paths relative to the reference repository root).
+ *
+ * Call order:  sart_create -> [sart_comm_init if nranks > 1] -> sart_upload_rows* | sart_fill_synthetic
+ *              -> [sart_set_laplacian_coo] -> sart_finalize -> sart_solve* -> sart_destroy
+ * With nranks > 1 the calls marked COLLECTIVE must be made by every rank, in the same order.
+ */
+#ifndef SART_B200_H
+#define SART_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* error codes */
+#define SART_OK 0
+#define SART_ERR_INVALID_ARGUMENT 1 /* what the reference answers with a message + std::exit(1) */
+#define SART_ERR_CUDA 2
+#define SART_ERR_STATE 3 /* call order violated */
+#define SART_ERR_NCCL 4
+#define SART_ERR_NO_DEVICE 5
+
+/* solve status: BaseSARTSolverMPI::SUCCESS / MAX_ITERATIONS_EXCEEDED, source/sartsolver.cpp:16-17 */
+#define SART_STATUS_SUCCESS 0
+#define SART_STATUS_MAX_ITERATIONS_EXCEEDED (-1)
+
+/* Where the reference's CPU and GPU solvers differ observably (initial guess over saturated pixels,
+ * source/sartsolver.cpp:153 vs source/cuda/sart_kernels.cu:33-34; 1e-7 floor on the starting solution,
+ * source/sartsolver_cuda.cpp:180) the engine follows one or the other. Default: the CPU solver. */
+#define SART_SEMANTICS_CPU 0
+#define SART_SEMANTICS_GPU 1
+
+#define SART_UNIQUE_ID_BYTES 128
+
+typedef struct sart_engine sart_engine;
+
+/* Construction arguments: BaseSARTSolverMPICuda::BaseSARTSolverMPICuda(rtm, lm, rank, thresholds..., comm),
+ * source/include/sartsolver_cuda.hpp:31-35, plus the matrix extents the reference takes from RayTransferMatrix. */
+typedef struct sart_config {
+    uint64_t npixel;  /* TOTAL number of matrix rows over all ranks */
+    uint64_t nvoxel;  /* number of matrix columns (every rank holds all of them, source/main.cpp:76) */
+    int32_t rank;     /* this process's rank; it owns the rows sart_shard_range() gives */
+    int32_t nranks;   /* number of ranks (= GPUs) */
+    int32_t device;   /* CUDA ordinal, or -1 for rank % device_count (source/sartsolver_cuda.cpp:96-98) */
+    int32_t logarithmic;      /* 0: SARTSolverMPICuda, 1: LogSARTSolverMPICuda */
+    int32_t semantics;        /* SART_SEMANTICS_* */
+    int32_t max_iterations;   /* default 2000 */
+    int32_t fixed_iterations; /* 1: never test convergence, always run max_iterations (benchmark switch; not in the reference) */
+    int32_t reserved;
+    double ray_density_threshold; /* default 1e-6 */
+    double ray_length_threshold;  /* default 1e-6 */
+    double conv_tolerance;        /* default 1e-5 */
+    double beta_laplace;          /* default 1e-2 (the constructor default, source/include/sartsolver.hpp:55) */
+    double relaxation;            /* default 1 */
+} sart_config;
+
+/* Per-solve measurements kept by the engine (device time from CUDA events on the engine's own stream). */
+typedef struct sart_stats {
+    int32_t status;          /* of the last solve */
+    int32_t iterations;      /* passes through the reference's iteration loop the last solve made */
+    int32_t sweeps;          /* full passes over the shard: iterations + 1 forward and iterations back projections, + 1 for an initial guess */
+    int32_t gpu_launches;    /* kernels of this library launched by the last solve */
+    double solve_ms;         /* device time of the whole solve, copies in and out included */
+    double iterate_ms;       /* device time of the iteration loop only (first sweep .. last update) */
+    double fp_ms_avg;        /* mean duration of one forward-projection launch */
+    double bp_ms_avg;        /* mean duration of one back-projection launch */
+    int32_t fp_launches;     /* launches behind fp_ms_avg */
+    int32_t bp_launches;     /* launches behind bp_ms_avg */
+    uint64_t matrix_bytes;   /* npixel_local * nvoxel * 4: algorithmic bytes of ONE sweep of this shard */
+    uint64_t h2d_bytes;      /* host->device bytes moved by the last solve */
+    uint64_t d2h_bytes;      /* device->host bytes moved by the last solve */
+} sart_stats;
+
+typedef struct sart_device_info {
+    char name[256];
+    int32_t sm_count;
+    int32_t cc_major, cc_minor;
+    int32_t l2_bytes;
+    int32_t reserved;
+    uint64_t total_mem, free_mem;
+} sart_device_info;
+
+const char* sart_last_error(void);
+
+/* Defaults of the reference constructor (source/include/sartsolver_cuda.hpp:31-35), rank 0 of 1, device -1. */
+int sart_config_default(sart_config* cfg);
+
+/* The reference's row partition: offset_pixel / npixel_local of source/main.cpp:67-68. */
+int sart_shard_range(uint64_t npixel, int32_t nranks, int32_t rank, uint64_t* row_offset, uint64_t* nrows);
+
+int sart_device_query(int32_t device, sart_device_info* info);
+
+/* Replaces the constructor's device selection and allocations, source/sartsolver_cuda.cpp:78-126. Validates the
+ * six solver parameters like the setters below. Allocates the zero-filled shard [nrows][ld] fp32, ld = nvoxel
+ * rounded up to 32 floats so that every row starts on a 128-byte boundary. */
+int sart_create(const sart_config* cfg, sart_engine** out);
+int sart_destroy(sart_engine* e);
+
+/* Replaces MPI_Init / MPI_COMM_WORLD of source/main.cpp:63-65 for the engine's own reductions: rank 0 makes an
+ * id, the caller ships the 128 bytes to every rank by any means, then every rank calls sart_comm_init
+ * (COLLECTIVE; NCCL over NVLink, loaded with dlopen so a single-GPU caller needs no NCCL at all). */
+int sart_comm_unique_id(uint8_t id[SART_UNIQUE_ID_BYTES]);
+int sart_comm_init(sart_engine* e, const uint8_t id[SART_UNIQUE_ID_BYTES]);
+
+/* Replaces RayTransferMatrix::read_hdf5's row-at-a-time fill of the host matrix + the constructor's one
+ * cudaMemcpy (source/raytransfer.cpp:92-110, source/sartsolver_cuda.cpp:104-106): copies the block
+ * rows [local_row0, +nrows) x columns [col0, +ncols) from src (row-major, leading dimension src_ld floats, pinned
+ * or pageable) straight into the shard. Arbitrary sub-blocks, because files come per camera x voxel segment.
+ * Returns after the copy has completed. */
+int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64_t col0, uint64_t ncols,
+                     const float* src, uint64_t src_ld);
+/* Test/bench helpers without a reference counterpart: counter-based synthetic matrix keyed by GLOBAL row and
+ * column (shard-invariant), and read-back of shard rows (dst leading dimension nvoxel). */
+int sart_fill_synthetic(sart_engine* e, uint64_t seed);
+int sart_download_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, float* dst);
+
+/* Replaces LaplacianMatrix (source/include/laplacian.hpp:15-19) as the solver sees it: COO entries with the
+ * flattened index i * nvoxel + j and fp32 values, any order (the reference sorts on load, source/laplacian.cpp:67-82).
+ * nnz == 0 clears it. With nranks > 1 the reference gives the matrix to rank 0 only (source/main.cpp:73-74);
+ * here sart_finalize broadcasts rank 0's copy so that every GPU can apply the penalty. */
+int sart_set_laplacian_coo(sart_engine* e, const uint64_t* flat_index, const float* value, uint64_t nnz);
+
+/* Replaces the base-class constructor's two host sweeps, source/sartsolver.cpp:35-56: ray_length (row sums of the
+ * local rows) and ray_density (column sums over ALL ranks' rows), accumulated in double on the device.
+ * COLLECTIVE. Must be called again after the matrix or the Laplacian changes. */
+int sart_finalize(sart_engine* e);
+int sart_get_ray_sums(sart_engine* e, double* ray_density /* [nvoxel] or NULL */, double* ray_length /* [nrows] or NULL */);
+
+/* Setters / getters with the reference's range checks, source/sartsolver.cpp:61-123
+ * (thresholds >= 0, tolerance > 0, beta >= 0, relaxation in (0, 1], max_iterations > 0). */
+int sart_set_ray_density_threshold(sart_engine* e, double v);
+int sart_set_ray_length_threshold(sart_engine* e, double v);
+int sart_set_convolution_tolerance(sart_engine* e, double v);
+int sart_set_beta_laplace(sart_engine* e, double v);
+int sart_set_relaxation(sart_engine* e, double v);
+int sart_set_max_iterations(sart_engine* e, int32_t v);
+int sart_set_fixed_iterations(sart_engine* e, int32_t on);
+int sart_get_config(const sart_engine* e, sart_config* out);
+
+/* Replaces SARTSolverMPICuda::solve / LogSARTSolverMPICuda::solve, source/sartsolver_cuda.cpp:197-274, 277-354
+ * (declared source/include/sartsolver.hpp:50-51). COLLECTIVE.
+ *   measurement  [nrows]  this rank's slice of the frame (host, double); negative = saturated pixel
+ *   solution     [nvoxel] host, double; in: starting solution when has_guess != 0; out: the solution
+ *   has_guess    0 = the reference's "solution.empty()": start from the default initial guess
+ *   status       SART_STATUS_*;  iterations: passes through the iteration loop (the reference does not report it) */
+int sart_solve(sart_engine* e, const double* measurement, double* solution, int32_t has_guess, int32_t* status,
+               int32_t* iterations);
+
+/* The same solve split at the host<->device copies, for callers that keep frames and solutions on the device
+ * (time series with warm start: the previous solution never leaves HBM). sart_solve == stage_measurement
+ * [+ stage_guess] + solve_resident + fetch_solution. */
+int sart_stage_measurement(sart_engine* e, const double* measurement);
+int sart_stage_guess(sart_engine* e, const double* solution);
+int sart_solve_resident(sart_engine* e, int32_t has_guess, int32_t* status, int32_t* iterations); /* COLLECTIVE */
+int sart_fetch_solution(sart_engine* e, double* solution);
+
+/* Synthetic frames without a reference counterpart: out[i] = sum_j H[i][j] * x[j] over the local rows, fp64
+ * accumulation on the device (what a camera would measure for emission x). */
+int sart_forward_project(sart_engine* e, const double* x, double* out);
+
+int sart_get_stats(const sart_engine* e, sart_stats* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SART_B200_H */

@@ -1,0 +1,908 @@
+// libsart_b200.so -- host side of the engine and the C ABI declared in include/sart_b200.h.
+//
+// What the reference spreads over BaseSARTSolverMPICuda's constructor, pre_iteration_setup and the two solve()
+// bodies (source/sartsolver_cuda.cpp:78-354) lives here as one engine object per process (= per GPU = per row
+// shard). All device memory is allocated once per engine (the reference allocates and frees five vectors per
+// frame, sartsolver_cuda.cpp:160-191, 223, 267-271); a solve is a fixed sequence of launches on one stream with the
+// convergence decision taken on the device, polled by the host once per batch of sweeps.
+// There is no CPU fallback: without a CUDA device sart_create fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "../../include/sart_b200.h"
+#include "kernels.cuh"
+#include "nccl_dyn.h"
+
+using namespace sart;
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                       \
+    do {                                                                                                     \
+        cudaError_t err__ = (expr);                                                                          \
+        if (err__ != cudaSuccess)                                                                            \
+            return fail(SART_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(err__) + " at " +    \
+                                           __FILE__ + ":" + std::to_string(__LINE__) + " (" #expr ")");      \
+    } while (0)
+
+#define NCCL_TRY(api, expr)                                                                                  \
+    do {                                                                                                     \
+        ncclResult_t r__ = (expr);                                                                           \
+        if (r__ != ncclSuccess)                                                                              \
+            return fail(SART_ERR_NCCL, std::string("NCCL error: ") + (api)->GetErrorString(r__) + " at " +   \
+                                           __FILE__ + ":" + std::to_string(__LINE__));                       \
+    } while (0)
+
+#define SART_TRY(expr)          \
+    do {                        \
+        int rc__ = (expr);      \
+        if (rc__) return rc__;  \
+    } while (0)
+
+constexpr int kProfiledSweeps = 64;  // sweeps per solve whose kernels are bracketed by events
+constexpr int kBpThreads = 256;
+constexpr int kFpThreads = 256;
+
+int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return (v && *v) ? std::atoi(v) : dflt;
+}
+
+inline uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+// messages of the reference's setters, source/sartsolver.cpp:63-123
+int check_params(const sart_config& c) {
+    if (!(c.ray_density_threshold >= 0)) return fail(SART_ERR_INVALID_ARGUMENT, "Ray density threshold must be non-negative.");
+    if (!(c.ray_length_threshold >= 0)) return fail(SART_ERR_INVALID_ARGUMENT, "Ray length threshold must be non-negative.");
+    if (!(c.conv_tolerance > 0)) return fail(SART_ERR_INVALID_ARGUMENT, "Convolution tolerance must be positive.");
+    if (!(c.beta_laplace >= 0)) return fail(SART_ERR_INVALID_ARGUMENT, "Attribute beta_laplace must be non-negative.");
+    if (!(c.relaxation > 0) || c.relaxation > 1.) return fail(SART_ERR_INVALID_ARGUMENT, "Attribute relaxation must be within (0, 1] interval.");
+    if (c.max_iterations <= 0) return fail(SART_ERR_INVALID_ARGUMENT, "Attribute max_iterations must be positive.");
+    return SART_OK;
+}
+
+}  // namespace
+
+struct sart_engine {
+    sart_config cfg{};
+    int device = 0, sm_count = 0;
+    cudaStream_t stream = nullptr;
+    uint64_t row_offset = 0, P = 0, V = 0, ld = 0, ld4 = 0;
+
+    float* dH = nullptr;
+    double *d_rho = nullptr, *d_lambda = nullptr;
+    bool finalized = false;
+
+    std::vector<uint64_t> lap_idx;
+    std::vector<float> lap_val;
+    int *d_lap_rowptr = nullptr, *d_lap_col = nullptr;
+    float* d_lap_val = nullptr;
+    uint64_t lap_nnz = 0;
+
+    double *d_gd = nullptr, *d_xio = nullptr, *d_obs = nullptr, *d_sred = nullptr, *d_f2part = nullptr, *d_f2 = nullptr;
+    double* d_xd[2] = {nullptr, nullptr};
+    float* d_xf[2] = {nullptr, nullptr};
+    float *d_g = nullptr, *d_rinv = nullptr, *d_fit = nullptr, *d_w = nullptr, *d_part = nullptr;
+    FrameScalars* d_fs = nullptr;
+    IterState* d_st[2] = {nullptr, nullptr};
+    IterState* h_st = nullptr;  // pinned, 2 slots
+
+    // launch geometry
+    uint32_t bp_panels = 0, bp_slabs = 0, bp_rows_per_slab = 0;
+    uint32_t fp_grid = 0, fp_nrg = 0;
+    int fp_variant = 0, bp_variant = 0, fp_rows = 8;
+    int batch = 1;
+
+    cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
+    cudaEvent_t ev_batch[2] = {nullptr, nullptr};
+    cudaEvent_t ev_prof[kProfiledSweeps][4];  // before/after FP, before/after BP
+    bool profiling = true;
+
+    ncclComm_t comm = nullptr;
+    bool measurement_staged = false, guess_staged = false;
+    int launches = 0;
+    sart_stats stats{};
+
+    sart_engine() {
+        for (auto& s : ev_prof) s[0] = s[1] = s[2] = s[3] = nullptr;
+    }
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(T** p, uint64_t count, bool zero = true) {
+    CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(p), std::max<uint64_t>(count, 1) * sizeof(T)));
+    if (zero) CUDA_TRY(cudaMemset(*p, 0, std::max<uint64_t>(count, 1) * sizeof(T)));
+    return SART_OK;
+}
+
+// ---- launchers ------------------------------------------------------------------------------------------------------
+
+typedef void (*FpKernel)(const FpArgs);
+typedef void (*BpKernel)(const BpArgs);
+
+struct FpVariant {
+    FpKernel fn;
+    int rows;
+    const char* name;
+};
+struct BpVariant {
+    BpKernel fn;
+    int threads;
+    const char* name;
+};
+
+const FpVariant kFpVariants[] = {
+    {fp_rows_kernel<8, kFpThreads, 2>, 8, "R8xU2"},
+    {fp_rows_kernel<4, kFpThreads, 4>, 4, "R4xU4"},
+    {fp_rows_kernel<8, kFpThreads, 1>, 8, "R8xU1"},
+    {fp_rows_kernel<4, kFpThreads, 2>, 4, "R4xU2"},
+};
+const BpVariant kBpVariants[] = {
+    {bp_cols_kernel<kBpThreads, 8>, kBpThreads, "T256xU8"},
+    {bp_cols_kernel<kBpThreads, 16>, kBpThreads, "T256xU16"},
+    {bp_cols_kernel<128, 8>, 128, "T128xU8"},
+    {bp_cols_kernel<128, 16>, 128, "T128xU16"},
+};
+constexpr int kNumFpVariants = sizeof(kFpVariants) / sizeof(kFpVariants[0]);
+constexpr int kNumBpVariants = sizeof(kBpVariants) / sizeof(kBpVariants[0]);
+
+int plan_launches(sart_engine* e) {
+    e->fp_variant = std::min(std::max(env_int("SART_FP_VARIANT", 0), 0), kNumFpVariants - 1);
+    e->bp_variant = std::min(std::max(env_int("SART_BP_VARIANT", 0), 0), kNumBpVariants - 1);
+    const FpVariant& fv = kFpVariants[e->fp_variant];
+    const BpVariant& bv = kBpVariants[e->bp_variant];
+
+    int fp_occ = 0, bp_occ = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, fv.fn, kFpThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, bv.fn, bv.threads, 0));
+    fp_occ = std::max(fp_occ, 1);
+    bp_occ = std::max(bp_occ, 1);
+
+    e->fp_rows = fv.rows;
+    e->fp_nrg = (uint32_t)ceil_div(e->P, fv.rows);
+    const int fp_ctas_per_sm = env_int("SART_FP_CTAS_PER_SM", fp_occ);
+    e->fp_grid = (uint32_t)std::min<uint64_t>(e->fp_nrg, (uint64_t)e->sm_count * std::max(fp_ctas_per_sm, 1));
+
+    // back projection: one wave of (panels x slabs) CTAs, slabs a multiple of 32 rows
+    e->bp_panels = (uint32_t)ceil_div(e->ld4, bv.threads);
+    const uint64_t target = (uint64_t)e->sm_count * std::max(env_int("SART_BP_CTAS_PER_SM", bp_occ), 1);
+    uint64_t slabs = std::max<uint64_t>(1, target / e->bp_panels);
+    const int forced = env_int("SART_BP_SLABS", 0);
+    if (forced > 0) slabs = (uint64_t)forced;
+    slabs = std::min<uint64_t>(slabs, ceil_div(e->P, 32));
+    e->bp_rows_per_slab = (uint32_t)(ceil_div(ceil_div(e->P, slabs), 32) * 32);
+    e->bp_slabs = (uint32_t)ceil_div(e->P, e->bp_rows_per_slab);
+
+    // sweeps per status poll: enough work per poll that the host round trip hides behind the next batch
+    const double sweep_us = 2.0 * (double)e->P * (double)e->ld * 4.0 / 6.0e6;  // at ~6 TB/s
+    e->batch = std::min(16, std::max(1, (int)std::ceil(400.0 / std::max(sweep_us, 1.0))));
+    e->batch = std::max(1, env_int("SART_BATCH", e->batch));
+    return SART_OK;
+}
+
+int launch_fp(sart_engine* e, const float* x, const IterState* st) {
+    FpArgs a;
+    a.H = e->dH;
+    a.ld4 = e->ld4;
+    a.P = e->P;
+    a.x = x;
+    a.g = e->d_g;
+    a.rinv = e->d_rinv;
+    a.fit = e->d_fit;
+    a.w = e->d_w;
+    a.f2part = e->d_f2part;
+    a.st = st;
+    a.nrg = e->fp_nrg;
+    a.log_mode = e->cfg.logarithmic;
+    kFpVariants[e->fp_variant].fn<<<e->fp_grid, kFpThreads, 0, e->stream>>>(a);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+int launch_bp(sart_engine* e, const IterState* st) {
+    BpArgs a;
+    a.H = e->dH;
+    a.ld4 = e->ld4;
+    a.P = e->P;
+    a.w = e->d_w;
+    a.part = e->d_part;
+    a.rows_per_slab = e->bp_rows_per_slab;
+    a.st = st;
+    const BpVariant& bv = kBpVariants[e->bp_variant];
+    bv.fn<<<dim3(e->bp_panels, e->bp_slabs), bv.threads, 0, e->stream>>>(a);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+int launch_reduce(sart_engine* e, const IterState* st) {
+    const uint32_t blocks = (uint32_t)ceil_div(e->V, 256);
+    reduce_partials_kernel<<<blocks, 256, 0, e->stream>>>(e->d_part, e->bp_slabs, e->ld, e->V, e->d_sred, st);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+int allreduce_f64(sart_engine* e, double* buf, uint64_t count, ncclRedOp_t op) {
+    if (e->cfg.nranks <= 1) return SART_OK;
+    NcclApi* api = nccl_api();
+    if (!api || !e->comm) return fail(SART_ERR_STATE, "nranks > 1 but sart_comm_init has not been called");
+    NCCL_TRY(api, api->AllReduce(buf, buf, count, ncclDouble, op, e->comm, e->stream));
+    return SART_OK;
+}
+
+// One sweep for the iterate x_t: forward projection, decision, and -- unless t is the last possible sweep, where
+// the decision can only be "stop" -- back projection, reduction and update. Kernels after the decision test the
+// freshly written state, so nothing but the forward projection runs once the solve is over.
+int enqueue_sweep(sart_engine* e, int t) {
+    const IterState* st_in = e->d_st[t & 1];
+    IterState* st_out = e->d_st[(t + 1) & 1];
+    const bool prof = e->profiling && t < kProfiledSweeps;
+    const bool last = t >= e->cfg.max_iterations;
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
+    SART_TRY(launch_fp(e, e->d_xf[t & 1], st_in));
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
+
+    DecideArgs d;
+    d.f2part = e->d_f2part;
+    d.n = e->fp_grid;
+    if (e->cfg.nranks > 1) {
+        f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_f2part, e->fp_grid, e->d_f2, st_in);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+        SART_TRY(allreduce_f64(e, e->d_f2, 1, ncclSum));
+        d.f2part = e->d_f2;
+        d.n = 1;
+    }
+    d.fs = e->d_fs;
+    d.st_in = st_in;
+    d.st_out = st_out;
+    d.tol = e->cfg.conv_tolerance;
+    d.max_iter = e->cfg.max_iterations;
+    d.fixed = e->cfg.fixed_iterations;
+    d.t = t;
+    decide_kernel<<<1, 32, 0, e->stream>>>(d);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    if (last) return SART_OK;
+
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+    SART_TRY(launch_bp(e, st_out));
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+    SART_TRY(launch_reduce(e, st_out));
+    SART_TRY(allreduce_f64(e, e->d_sred, e->V, ncclSum));
+
+    UpdArgs u;
+    u.sred = e->d_sred;
+    u.xd_cur = e->d_xd[t & 1];
+    u.xd_next = e->d_xd[(t + 1) & 1];
+    u.xf_next = e->d_xf[(t + 1) & 1];
+    u.ray_density = e->d_rho;
+    u.obs = e->d_obs;
+    u.lap_rowptr = e->lap_nnz ? e->d_lap_rowptr : nullptr;
+    u.lap_col = e->d_lap_col;
+    u.lap_val = e->d_lap_val;
+    u.fs = e->d_fs;
+    u.st = st_out;
+    u.V = e->V;
+    u.beta = e->cfg.beta_laplace;
+    u.relax = e->cfg.relaxation;
+    u.h_d = e->cfg.ray_density_threshold;
+    u.eps_norm = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 1.e-7 : 0.0;
+    u.eps_orig = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 0.0 : 1.e-100;
+    u.log_mode = e->cfg.logarithmic;
+    update_kernel<<<(uint32_t)ceil_div(e->V, 256), 256, 0, e->stream>>>(u);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+// column reduction of the staged weights d_w into d_sred (reduced over ranks): initial guess / log-solver "obs"
+int backproject_weights(sart_engine* e) {
+    SART_TRY(launch_bp(e, nullptr));
+    SART_TRY(launch_reduce(e, nullptr));
+    SART_TRY(allreduce_f64(e, e->d_sred, e->V, ncclSum));
+    return SART_OK;
+}
+
+int launch_prepare(sart_engine* e, int weights_mode) {
+    frame_prepare_kernel<<<(uint32_t)ceil_div(e->P, 256), 256, 0, e->stream>>>(
+        e->d_gd, e->P, e->d_fs, e->d_lambda, e->cfg.ray_length_threshold, e->d_g, e->d_rinv, e->d_w, weights_mode);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+// The whole solve from device-resident inputs (d_gd, and d_xio when has_guess) to device-resident output (d_xio).
+int run_solve(sart_engine* e, int has_guess) {
+    const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
+    const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
+    const bool log_mode = e->cfg.logarithmic != 0;
+
+    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_gd, e->P, e->d_fs);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    SART_TRY(allreduce_f64(e, &e->d_fs->gmax, 1, ncclMax));
+    SART_TRY(allreduce_f64(e, &e->d_fs->gsq, 1, ncclSum));
+
+    int sweeps = 0;
+    if (log_mode) {
+        SART_TRY(launch_prepare(e, 3));
+        SART_TRY(backproject_weights(e));
+        mask_obs_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_rho, e->cfg.ray_density_threshold, e->d_obs, e->V);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+        ++sweeps;
+    }
+    SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1)));
+    if (!has_guess) {
+        SART_TRY(backproject_weights(e));
+        ++sweeps;
+    }
+    // lower clamp of the starting solution: GPU semantics 1e-7 (normalised units) for both solvers
+    // (sartsolver_cuda.cpp:180); CPU semantics 1e-100 (caller units) for the log solver only (sartsolver.cpp:263)
+    const double floor_norm = gpu_sem ? 1.e-7 : 0.0;
+    const double floor_orig = (!gpu_sem && log_mode) ? 1.e-100 : 0.0;
+    start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_xio, e->d_rho, e->cfg.ray_density_threshold,
+                                                          e->d_fs, floor_norm, floor_orig, has_guess, e->d_xd[0],
+                                                          e->d_xf[0], e->V);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_st[0], e->d_st[1]);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
+
+    // Sweeps t = 0 .. max_iterations. Batches are enqueued one ahead of the status poll, so the device never
+    // waits for the host; launches that arrive after the device has decided to stop return immediately.
+    const int t_max = e->cfg.max_iterations;
+    int t = 0, slot = 0, done_slot = -1;
+    std::deque<int> in_flight;
+    while (true) {
+        if (t <= t_max) {
+            const int nb = std::min(e->batch, t_max - t + 1);
+            for (int i = 0; i < nb; ++i) SART_TRY(enqueue_sweep(e, t + i));
+            t += nb;
+            CUDA_TRY(cudaMemcpyAsync(&e->h_st[slot], e->d_st[t & 1], sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaEventRecord(e->ev_batch[slot], e->stream));
+            in_flight.push_back(slot);
+            slot ^= 1;
+        }
+        if (in_flight.size() == 2 || t > t_max) {
+            if (in_flight.empty()) return fail(SART_ERR_STATE, "solve ended without a decision (internal error)");
+            const int s = in_flight.front();
+            in_flight.pop_front();
+            CUDA_TRY(cudaEventSynchronize(e->ev_batch[s]));
+            if (e->h_st[s].done) {
+                done_slot = s;
+                break;
+            }
+        }
+    }
+    const IterState fin = e->h_st[done_slot];
+
+    finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_xd[0], e->d_xd[1], e->d_st[t & 1], e->d_fs, e->d_xio, e->V);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+
+    e->stats.status = fin.status;
+    e->stats.iterations = fin.iterations;
+    e->stats.sweeps = sweeps + 2 * fin.iterations + 1;
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_it0, e->ev_batch[done_slot]));
+    e->stats.iterate_ms = ms;
+    e->stats.fp_ms_avg = e->stats.bp_ms_avg = 0;
+    e->stats.fp_launches = e->stats.bp_launches = 0;
+    if (e->profiling) {
+        // every profiled sweep up to the deciding one has completed (they precede ev_batch[done_slot]); the deciding
+        // sweep ran its forward projection only
+        const int nfp = std::min(kProfiledSweeps, fin.iterations + 1);
+        const int nbp = std::min(kProfiledSweeps, fin.iterations);
+        double fp = 0, bp = 0;
+        for (int k = 0; k < nfp; ++k) {
+            float a = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][0], e->ev_prof[k][1]));
+            fp += a;
+        }
+        for (int k = 0; k < nbp; ++k) {
+            float b = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&b, e->ev_prof[k][2], e->ev_prof[k][3]));
+            bp += b;
+        }
+        e->stats.fp_ms_avg = nfp ? fp / nfp : 0;
+        e->stats.bp_ms_avg = nbp ? bp / nbp : 0;
+        e->stats.fp_launches = nfp;
+        e->stats.bp_launches = nbp;
+    }
+    return SART_OK;
+}
+
+int build_laplacian(sart_engine* e) {
+    // with several ranks the reference hands the matrix to rank 0 only (source/main.cpp:73-74): share rank 0's copy
+    if (e->cfg.nranks > 1) {
+        NcclApi* api = nccl_api();
+        if (!api || !e->comm) return fail(SART_ERR_STATE, "nranks > 1 but sart_comm_init has not been called");
+        unsigned long long* d_n = nullptr;
+        SART_TRY(dev_alloc(&d_n, 1));
+        unsigned long long n = e->lap_idx.size();
+        CUDA_TRY(cudaMemcpyAsync(d_n, &n, sizeof(n), cudaMemcpyHostToDevice, e->stream));
+        NCCL_TRY(api, api->Broadcast(d_n, d_n, 1, ncclUint64, 0, e->comm, e->stream));
+        CUDA_TRY(cudaMemcpyAsync(&n, d_n, sizeof(n), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(cudaStreamSynchronize(e->stream));
+        CUDA_TRY(cudaFree(d_n));
+        if (n) {
+            unsigned long long* d_i = nullptr;
+            float* d_v = nullptr;
+            SART_TRY(dev_alloc(&d_i, n, false));
+            SART_TRY(dev_alloc(&d_v, n, false));
+            if (e->cfg.rank == 0) {
+                CUDA_TRY(cudaMemcpyAsync(d_i, e->lap_idx.data(), n * 8, cudaMemcpyHostToDevice, e->stream));
+                CUDA_TRY(cudaMemcpyAsync(d_v, e->lap_val.data(), n * 4, cudaMemcpyHostToDevice, e->stream));
+            }
+            NCCL_TRY(api, api->Broadcast(d_i, d_i, n, ncclUint64, 0, e->comm, e->stream));
+            NCCL_TRY(api, api->Broadcast(d_v, d_v, n, ncclFloat, 0, e->comm, e->stream));
+            e->lap_idx.resize(n);
+            e->lap_val.resize(n);
+            CUDA_TRY(cudaMemcpyAsync(e->lap_idx.data(), d_i, n * 8, cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaMemcpyAsync(e->lap_val.data(), d_v, n * 4, cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaStreamSynchronize(e->stream));
+            CUDA_TRY(cudaFree(d_i));
+            CUDA_TRY(cudaFree(d_v));
+        } else {
+            e->lap_idx.clear();
+            e->lap_val.clear();
+        }
+    }
+
+    if (e->d_lap_rowptr) cudaFree(e->d_lap_rowptr);
+    if (e->d_lap_col) cudaFree(e->d_lap_col);
+    if (e->d_lap_val) cudaFree(e->d_lap_val);
+    e->d_lap_rowptr = e->d_lap_col = nullptr;
+    e->d_lap_val = nullptr;
+    e->lap_nnz = e->lap_idx.size();
+    if (!e->lap_nnz) return SART_OK;
+
+    const uint64_t n = e->lap_nnz, V = e->V;
+    if (n > 0x7fffffffULL) return fail(SART_ERR_INVALID_ARGUMENT, "Laplacian has more than 2^31 entries");
+    std::vector<uint32_t> order(n);
+    std::iota(order.begin(), order.end(), 0u);
+    if (!std::is_sorted(e->lap_idx.begin(), e->lap_idx.end()))
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return e->lap_idx[a] < e->lap_idx[b]; });
+    std::vector<int> rowptr(V + 1, 0), col(n);
+    std::vector<float> val(n);
+    for (uint64_t k = 0; k < n; ++k) {
+        const uint64_t flat = e->lap_idx[order[k]];
+        const uint64_t i = flat / V, j = flat % V;
+        if (i >= V) return fail(SART_ERR_INVALID_ARGUMENT, "Laplacian index out of range for nvoxel");
+        ++rowptr[i + 1];
+        col[k] = (int)j;
+        val[k] = e->lap_val[order[k]];
+    }
+    for (uint64_t i = 0; i < V; ++i) rowptr[i + 1] += rowptr[i];
+    SART_TRY(dev_alloc(&e->d_lap_rowptr, V + 1, false));
+    SART_TRY(dev_alloc(&e->d_lap_col, n, false));
+    SART_TRY(dev_alloc(&e->d_lap_val, n, false));
+    CUDA_TRY(cudaMemcpy(e->d_lap_rowptr, rowptr.data(), (V + 1) * sizeof(int), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(e->d_lap_col, col.data(), n * sizeof(int), cudaMemcpyHostToDevice));
+    CUDA_TRY(cudaMemcpy(e->d_lap_val, val.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    return SART_OK;
+}
+
+int require(sart_engine* e, bool finalized) {
+    if (!e) return fail(SART_ERR_INVALID_ARGUMENT, "engine is NULL");
+    CUDA_TRY(cudaSetDevice(e->device));
+    if (finalized && !e->finalized) return fail(SART_ERR_STATE, "sart_finalize has not been called");
+    return SART_OK;
+}
+
+void free_engine(sart_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    if (e->comm) {
+        NcclApi* api = nccl_api();
+        if (api) api->CommDestroy(e->comm);
+    }
+    void* ptrs[] = {e->dH, e->d_rho, e->d_lambda, e->d_lap_rowptr, e->d_lap_col, e->d_lap_val, e->d_gd, e->d_xio,
+                    e->d_obs, e->d_sred, e->d_f2part, e->d_f2, e->d_xd[0], e->d_xd[1], e->d_xf[0], e->d_xf[1], e->d_g,
+                    e->d_rinv, e->d_fit, e->d_w, e->d_part, e->d_fs, e->d_st[0], e->d_st[1]};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (e->h_st) cudaFreeHost(e->h_st);
+    cudaEvent_t evs[] = {e->ev_solve0, e->ev_solve1, e->ev_it0, e->ev_batch[0], e->ev_batch[1]};
+    for (cudaEvent_t ev : evs)
+        if (ev) cudaEventDestroy(ev);
+    for (auto& s : e->ev_prof)
+        for (int k = 0; k < 4; ++k)
+            if (s[k]) cudaEventDestroy(s[k]);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int create_impl(const sart_config* cfg, sart_engine* e) {
+    e->cfg = *cfg;
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess || count == 0)
+        return fail(SART_ERR_NO_DEVICE, std::string("no CUDA device available (") +
+                                            (err != cudaSuccess ? cudaGetErrorString(err) : "device count 0") +
+                                            "); this engine has no CPU path");
+    e->device = (cfg->device >= 0) ? cfg->device : cfg->rank % count;  // sartsolver_cuda.cpp:96-98
+    if (e->device >= count) return fail(SART_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    CUDA_TRY(cudaSetDevice(e->device));
+    CUDA_TRY(cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, e->device));
+    CUDA_TRY(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+
+    SART_TRY(sart_shard_range(cfg->npixel, cfg->nranks, cfg->rank, &e->row_offset, &e->P));
+    e->V = cfg->nvoxel;
+    e->ld = ceil_div(e->V, 32) * 32;
+    e->ld4 = e->ld / 4;
+    if (e->P == 0) return fail(SART_ERR_INVALID_ARGUMENT, "this rank owns no rows (nranks > npixel)");
+    if (e->ld4 * 8 >= (1ull << 32)) return fail(SART_ERR_INVALID_ARGUMENT, "nvoxel too large");
+    e->cfg.device = e->device;
+
+    SART_TRY(plan_launches(e));
+
+    size_t free_b = 0, total_b = 0;
+    CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
+    const uint64_t need = e->P * e->ld * 4;
+    if (need + (512ull << 20) > free_b)
+        return fail(SART_ERR_CUDA, "matrix shard of " + std::to_string(need >> 20) + " MiB does not fit in the " +
+                                       std::to_string(free_b >> 20) + " MiB free on device " + std::to_string(e->device));
+    SART_TRY(dev_alloc(&e->dH, e->P * e->ld));
+    SART_TRY(dev_alloc(&e->d_rho, e->V));
+    SART_TRY(dev_alloc(&e->d_lambda, e->P));
+    SART_TRY(dev_alloc(&e->d_gd, e->P));
+    SART_TRY(dev_alloc(&e->d_xio, e->V));
+    SART_TRY(dev_alloc(&e->d_obs, e->V));
+    SART_TRY(dev_alloc(&e->d_sred, e->V + 2));
+    SART_TRY(dev_alloc(&e->d_f2part, (uint64_t)e->sm_count * 32));
+    SART_TRY(dev_alloc(&e->d_f2, 1));
+    for (int k = 0; k < 2; ++k) {
+        SART_TRY(dev_alloc(&e->d_xd[k], e->V));
+        SART_TRY(dev_alloc(&e->d_xf[k], e->ld));
+        SART_TRY(dev_alloc(&e->d_st[k], 1));
+    }
+    SART_TRY(dev_alloc(&e->d_g, e->P));
+    SART_TRY(dev_alloc(&e->d_rinv, e->P));
+    SART_TRY(dev_alloc(&e->d_fit, e->P));
+    SART_TRY(dev_alloc(&e->d_w, e->P));
+    SART_TRY(dev_alloc(&e->d_part, (uint64_t)e->bp_slabs * e->ld));
+    SART_TRY(dev_alloc(&e->d_fs, 1));
+    CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_st), 2 * sizeof(IterState)));
+
+    CUDA_TRY(cudaEventCreate(&e->ev_solve0));
+    CUDA_TRY(cudaEventCreate(&e->ev_solve1));
+    CUDA_TRY(cudaEventCreate(&e->ev_it0));
+    CUDA_TRY(cudaEventCreate(&e->ev_batch[0]));
+    CUDA_TRY(cudaEventCreate(&e->ev_batch[1]));
+    e->profiling = env_int("SART_PROFILE_KERNELS", 1) != 0;
+    if (e->profiling)
+        for (auto& s : e->ev_prof)
+            for (int k = 0; k < 4; ++k) CUDA_TRY(cudaEventCreate(&s[k]));
+    e->stats.matrix_bytes = e->P * e->V * 4;
+    CUDA_TRY(cudaDeviceSynchronize());
+    return SART_OK;
+}
+
+}  // namespace
+
+// ---- C ABI ----------------------------------------------------------------------------------------------------------
+
+extern "C" {
+
+const char* sart_last_error(void) { return g_error.c_str(); }
+
+int sart_config_default(sart_config* cfg) {
+    if (!cfg) return fail(SART_ERR_INVALID_ARGUMENT, "cfg is NULL");
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->nranks = 1;
+    cfg->device = -1;
+    cfg->semantics = SART_SEMANTICS_CPU;
+    cfg->max_iterations = 2000;
+    cfg->ray_density_threshold = 1.e-6;
+    cfg->ray_length_threshold = 1.e-6;
+    cfg->conv_tolerance = 1.e-5;
+    cfg->beta_laplace = 1.e-2;
+    cfg->relaxation = 1.;
+    return SART_OK;
+}
+
+int sart_shard_range(uint64_t npixel, int32_t nranks, int32_t rank, uint64_t* row_offset, uint64_t* nrows) {
+    if (nranks < 1 || rank < 0 || rank >= nranks || !row_offset || !nrows)
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_shard_range: need 0 <= rank < nranks and non-NULL outputs");
+    const uint64_t n = (uint64_t)nranks, r = (uint64_t)rank;
+    const uint64_t base = npixel / n, rem = npixel % n;
+    *row_offset = r * base + std::min(r, rem);
+    *nrows = (r < rem) ? base + 1 : base;
+    return SART_OK;
+}
+
+int sart_device_query(int32_t device, sart_device_info* info) {
+    if (!info) return fail(SART_ERR_INVALID_ARGUMENT, "info is NULL");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count)
+        return fail(SART_ERR_NO_DEVICE, "no such CUDA device");
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    std::memset(info, 0, sizeof(*info));
+    std::snprintf(info->name, sizeof(info->name), "%s", prop.name);
+    info->sm_count = prop.multiProcessorCount;
+    info->cc_major = prop.major;
+    info->cc_minor = prop.minor;
+    info->l2_bytes = prop.l2CacheSize;
+    CUDA_TRY(cudaSetDevice(device));
+    size_t f = 0, t = 0;
+    CUDA_TRY(cudaMemGetInfo(&f, &t));
+    info->free_mem = f;
+    info->total_mem = t;
+    return SART_OK;
+}
+
+int sart_create(const sart_config* cfg, sart_engine** out) {
+    if (!cfg || !out) return fail(SART_ERR_INVALID_ARGUMENT, "cfg or out is NULL");
+    *out = nullptr;
+    if (cfg->npixel == 0 || cfg->nvoxel == 0) return fail(SART_ERR_INVALID_ARGUMENT, "npixel and nvoxel must be positive");
+    if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks) return fail(SART_ERR_INVALID_ARGUMENT, "need 0 <= rank < nranks");
+    if (cfg->semantics != SART_SEMANTICS_CPU && cfg->semantics != SART_SEMANTICS_GPU) return fail(SART_ERR_INVALID_ARGUMENT, "unknown semantics");
+    SART_TRY(check_params(*cfg));
+    sart_engine* e = new sart_engine();
+    const int rc = create_impl(cfg, e);
+    if (rc) {
+        const std::string keep = g_error;
+        free_engine(e);
+        g_error = keep;
+        return rc;
+    }
+    *out = e;
+    return SART_OK;
+}
+
+int sart_destroy(sart_engine* e) {
+    free_engine(e);
+    return SART_OK;
+}
+
+int sart_comm_unique_id(uint8_t id[SART_UNIQUE_ID_BYTES]) {
+    static_assert(sizeof(ncclUniqueId) == SART_UNIQUE_ID_BYTES, "ncclUniqueId size");
+    NcclApi* api = nccl_api();
+    if (!api) return fail(SART_ERR_NCCL, nccl_storage().error);
+    ncclUniqueId uid;
+    NCCL_TRY(api, api->GetUniqueId(&uid));
+    std::memcpy(id, &uid, sizeof(uid));
+    return SART_OK;
+}
+
+int sart_comm_init(sart_engine* e, const uint8_t id[SART_UNIQUE_ID_BYTES]) {
+    SART_TRY(require(e, false));
+    if (e->cfg.nranks <= 1) return SART_OK;
+    if (e->comm) return fail(SART_ERR_STATE, "communicator already initialised");
+    NcclApi* api = nccl_api();
+    if (!api) return fail(SART_ERR_NCCL, nccl_storage().error);
+    ncclUniqueId uid;
+    std::memcpy(&uid, id, sizeof(uid));
+    NCCL_TRY(api, api->CommInitRank(&e->comm, e->cfg.nranks, uid, e->cfg.rank));
+    return SART_OK;
+}
+
+int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64_t col0, uint64_t ncols,
+                     const float* src, uint64_t src_ld) {
+    SART_TRY(require(e, false));
+    if (!src || local_row0 + nrows > e->P || col0 + ncols > e->V || src_ld < ncols)
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_upload_rows: block outside the shard or src_ld < ncols");
+    if (nrows == 0 || ncols == 0) return SART_OK;
+    CUDA_TRY(cudaMemcpy2DAsync(e->dH + local_row0 * e->ld + col0, e->ld * sizeof(float), src, src_ld * sizeof(float),
+                               ncols * sizeof(float), nrows, cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->finalized = false;
+    return SART_OK;
+}
+
+int sart_fill_synthetic(sart_engine* e, uint64_t seed) {
+    SART_TRY(require(e, false));
+    const int exponent = (int)std::lround(std::log2((double)e->V * 98304.0));
+    const float scale = std::ldexp(1.0f, -exponent);
+    const dim3 grid((uint32_t)std::min<uint64_t>(ceil_div(e->ld4, 256), 64), (uint32_t)std::min<uint64_t>(e->P, 32768));
+    fill_synthetic_kernel<<<grid, 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, e->row_offset, seed, scale);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->finalized = false;
+    return SART_OK;
+}
+
+int sart_download_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, float* dst) {
+    SART_TRY(require(e, false));
+    if (!dst || local_row0 + nrows > e->P) return fail(SART_ERR_INVALID_ARGUMENT, "sart_download_rows: rows outside the shard");
+    if (nrows == 0) return SART_OK;
+    CUDA_TRY(cudaMemcpy2DAsync(dst, e->V * sizeof(float), e->dH + local_row0 * e->ld, e->ld * sizeof(float),
+                               e->V * sizeof(float), nrows, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return SART_OK;
+}
+
+int sart_set_laplacian_coo(sart_engine* e, const uint64_t* flat_index, const float* value, uint64_t nnz) {
+    SART_TRY(require(e, false));
+    if (nnz && (!flat_index || !value)) return fail(SART_ERR_INVALID_ARGUMENT, "Laplacian arrays are NULL");
+    e->lap_idx.assign(flat_index, flat_index + nnz);
+    e->lap_val.assign(value, value + nnz);
+    e->finalized = false;
+    return SART_OK;
+}
+
+int sart_finalize(sart_engine* e) {
+    SART_TRY(require(e, false));
+    // ray_length_i: row sums of the local rows
+    forward_f64_kernel<<<(uint32_t)ceil_div(e->P, 8), 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, nullptr, e->d_lambda);
+    CUDA_TRY(cudaGetLastError());
+    // ray_density_j: column sums, slab partials then fixed-order sum, then over ranks
+    const uint32_t cblocks = (uint32_t)ceil_div(e->V, 256);
+    uint64_t slabs = std::max<uint64_t>(1, (uint64_t)e->sm_count * 8 / cblocks);
+    slabs = std::min<uint64_t>(slabs, e->P);
+    const uint32_t rows_per_slab = (uint32_t)ceil_div(e->P, slabs);
+    slabs = ceil_div(e->P, rows_per_slab);
+    double* d_part = nullptr;
+    SART_TRY(dev_alloc(&d_part, slabs * e->V, false));
+    col_sums_f64_kernel<<<dim3(cblocks, (uint32_t)slabs), 256, 0, e->stream>>>(e->dH, e->ld, e->P, e->V, rows_per_slab, d_part);
+    CUDA_TRY(cudaGetLastError());
+    reduce_f64_partials_kernel<<<cblocks, 256, 0, e->stream>>>(d_part, (uint32_t)slabs, e->V, e->d_rho);
+    CUDA_TRY(cudaGetLastError());
+    SART_TRY(allreduce_f64(e, e->d_rho, e->V, ncclSum));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    CUDA_TRY(cudaFree(d_part));
+    SART_TRY(build_laplacian(e));
+    e->finalized = true;
+    return SART_OK;
+}
+
+int sart_get_ray_sums(sart_engine* e, double* ray_density, double* ray_length) {
+    SART_TRY(require(e, true));
+    if (ray_density) CUDA_TRY(cudaMemcpy(ray_density, e->d_rho, e->V * sizeof(double), cudaMemcpyDeviceToHost));
+    if (ray_length) CUDA_TRY(cudaMemcpy(ray_length, e->d_lambda, e->P * sizeof(double), cudaMemcpyDeviceToHost));
+    return SART_OK;
+}
+
+#define SART_SETTER(name, field, type)                      \
+    int name(sart_engine* e, type v) {                      \
+        if (!e) return fail(SART_ERR_INVALID_ARGUMENT, "engine is NULL"); \
+        sart_config c = e->cfg;                             \
+        c.field = v;                                        \
+        SART_TRY(check_params(c));                          \
+        e->cfg.field = v;                                   \
+        return SART_OK;                                     \
+    }
+SART_SETTER(sart_set_ray_density_threshold, ray_density_threshold, double)
+SART_SETTER(sart_set_ray_length_threshold, ray_length_threshold, double)
+SART_SETTER(sart_set_convolution_tolerance, conv_tolerance, double)
+SART_SETTER(sart_set_beta_laplace, beta_laplace, double)
+SART_SETTER(sart_set_relaxation, relaxation, double)
+SART_SETTER(sart_set_max_iterations, max_iterations, int32_t)
+#undef SART_SETTER
+
+int sart_set_fixed_iterations(sart_engine* e, int32_t on) {
+    if (!e) return fail(SART_ERR_INVALID_ARGUMENT, "engine is NULL");
+    e->cfg.fixed_iterations = on ? 1 : 0;
+    return SART_OK;
+}
+
+int sart_get_config(const sart_engine* e, sart_config* out) {
+    if (!e || !out) return fail(SART_ERR_INVALID_ARGUMENT, "engine or out is NULL");
+    *out = e->cfg;
+    return SART_OK;
+}
+
+int sart_stage_measurement(sart_engine* e, const double* measurement) {
+    SART_TRY(require(e, true));
+    if (!measurement) return fail(SART_ERR_INVALID_ARGUMENT, "measurement is NULL");
+    CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurement, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->measurement_staged = true;
+    return SART_OK;
+}
+
+int sart_stage_guess(sart_engine* e, const double* solution) {
+    SART_TRY(require(e, true));
+    if (!solution) return fail(SART_ERR_INVALID_ARGUMENT, "solution is NULL");
+    CUDA_TRY(cudaMemcpyAsync(e->d_xio, solution, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    e->guess_staged = true;
+    return SART_OK;
+}
+
+int sart_solve_resident(sart_engine* e, int32_t has_guess, int32_t* status, int32_t* iterations) {
+    SART_TRY(require(e, true));
+    if (!e->measurement_staged) return fail(SART_ERR_STATE, "no measurement on the device (sart_stage_measurement)");
+    if (has_guess && !e->guess_staged) return fail(SART_ERR_STATE, "no starting solution on the device");
+    e->launches = 0;
+    CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
+    SART_TRY(run_solve(e, has_guess));
+    CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+    CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
+    e->stats.solve_ms = ms;
+    e->stats.gpu_launches = e->launches;
+    e->stats.h2d_bytes = e->stats.d2h_bytes = 0;
+    e->guess_staged = true;  // the solution stays on the device: the next frame may warm-start from it
+    if (status) *status = e->stats.status;
+    if (iterations) *iterations = e->stats.iterations;
+    return SART_OK;
+}
+
+int sart_fetch_solution(sart_engine* e, double* solution) {
+    SART_TRY(require(e, true));
+    if (!solution) return fail(SART_ERR_INVALID_ARGUMENT, "solution is NULL");
+    CUDA_TRY(cudaMemcpyAsync(solution, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return SART_OK;
+}
+
+int sart_solve(sart_engine* e, const double* measurement, double* solution, int32_t has_guess, int32_t* status,
+               int32_t* iterations) {
+    SART_TRY(require(e, true));
+    if (!measurement || !solution) return fail(SART_ERR_INVALID_ARGUMENT, "measurement or solution is NULL");
+    e->launches = 0;
+    CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurement, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    e->measurement_staged = true;
+    uint64_t h2d = e->P * sizeof(double);
+    if (has_guess) {
+        CUDA_TRY(cudaMemcpyAsync(e->d_xio, solution, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+        h2d += e->V * sizeof(double);
+    }
+    SART_TRY(run_solve(e, has_guess));
+    CUDA_TRY(cudaMemcpyAsync(solution, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+    CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
+    e->stats.solve_ms = ms;
+    e->stats.gpu_launches = e->launches;
+    e->stats.h2d_bytes = h2d;
+    e->stats.d2h_bytes = e->V * sizeof(double) + 2 * sizeof(IterState);
+    e->guess_staged = true;
+    if (status) *status = e->stats.status;
+    if (iterations) *iterations = e->stats.iterations;
+    return SART_OK;
+}
+
+int sart_forward_project(sart_engine* e, const double* x, double* out) {
+    SART_TRY(require(e, false));
+    if (!x || !out) return fail(SART_ERR_INVALID_ARGUMENT, "x or out is NULL");
+    double *d_x = nullptr, *d_o = nullptr;
+    SART_TRY(dev_alloc(&d_x, e->V, false));
+    SART_TRY(dev_alloc(&d_o, e->P, false));
+    CUDA_TRY(cudaMemcpyAsync(d_x, x, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    forward_f64_kernel<<<(uint32_t)ceil_div(e->P, 8), 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, d_x, d_o);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpyAsync(out, d_o, e->P * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    CUDA_TRY(cudaFree(d_x));
+    CUDA_TRY(cudaFree(d_o));
+    return SART_OK;
+}
+
+int sart_get_stats(const sart_engine* e, sart_stats* out) {
+    if (!e || !out) return fail(SART_ERR_INVALID_ARGUMENT, "engine or out is NULL");
+    *out = e->stats;
+    out->matrix_bytes = e->P * e->V * 4;
+    return SART_OK;
+}
+
+}  // extern "C"

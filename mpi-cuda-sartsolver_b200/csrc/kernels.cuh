@@ -1,0 +1,580 @@
+// Device code of the B200 constrained-SART engine (sm_100a).
+//
+// One SART iteration of the reference is (source/sartsolver_cuda.cpp:231-262, CPU twin source/sartsolver.cpp:180-229)
+//   penalty -> PropagateKernel (column reduction over H) -> host MPI_Allreduce -> UpdateSolutionKernel
+//   -> cublasSgemv (row reduction over H) -> cublasSdot -> host MPI_Allreduce -> host convergence test.
+// Here the same arithmetic is regrouped into one "sweep" per solution iterate x_t:
+//   forward projection  fit = H x_t  with the ray-length-normalised residual w and sum(fit^2) in its epilogue,
+//   decision            convergence test for x_t on the device (after an all-reduce of the scalar across row shards),
+//   back projection     s   = H^T w  (deterministic: per-slab partials, fixed-order reduction, no atomics),
+//   [all-reduce of s across row shards],
+//   update              x_{t+1} = max(x_t + alpha/rho * s - beta L x_t, 0)
+// so the only host involvement is a status poll every few sweeps. The matrix is streamed with 128-bit
+// L1-bypassing loads, fp32 FMAs, fp64 for every cross-thread / cross-CTA sum and for all scalars.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace sart {
+
+constexpr unsigned FULL_MASK = 0xffffffffu;
+
+// Device-resident control block of one solve; two copies, ping-ponged by sweep parity so that a kernel never
+// reads the copy another block of the same launch writes.
+struct IterState {
+    double conv_prev;  // convergence value of the previous reference iteration (sartsolver.cpp:179, 228)
+    int k;             // solution updates applied so far == index of the sweep that evaluates the current iterate
+    int done;          // 1: the solve is over, every later launch returns at once
+    int status;        // SART_STATUS_* once done
+    int iterations;    // passes through the reference's iteration loop
+    int final_buf;     // which of the two solution buffers holds the answer
+    int pad;
+};
+
+struct FrameScalars {
+    double gmax;  // max_i g_i over all ranks (sartsolver_cuda.cpp:147-149)
+    double gsq;   // sum over g_i > 0 of g_i^2 over all ranks (sartsolver.cpp:161-164)
+    double norm;  // gmax, or 1 when gmax <= 0
+    double m2;    // gsq / norm^2 (sartsolver_cuda.cpp:157)
+};
+
+__device__ __forceinline__ float4 ldg_stream(const float4* p) {
+    float4 r;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+        : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+        : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+    return v;
+}
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(FULL_MASK, v, o));
+    return v;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Forward projection: fit_i = sum_j H_ij x_j over the local rows  (replaces cublasSgemv, sartsolver_cuda.cpp:188-189,
+// 248-249; CPU twin sartsolver.cpp:166-173, 213-220), with in its epilogue
+//   w_i     = [lambda_i > h_l][g_i >= 0] (g_i - fit_i) / lambda_i        (prologue of PropagateKernel, sart_kernels.cu:75-82)
+//   or, log solver:  [..][..] fit_i / lambda_i                            (LogPropagateKernel, sart_kernels.cu:126-140)
+//   sum_i fit_i^2 over ALL rows, one fp64 partial per CTA                 (replaces cublasSdot, sartsolver_cuda.cpp:251-253)
+// A CTA owns R full rows at a time (persistent, strided over row groups). Every thread keeps R fp32 accumulators,
+// loads one float4 of x per column step and R float4 of H against it, UNROLL steps in flight.
+// ---------------------------------------------------------------------------------------------------------------------
+struct FpArgs {
+    const float* H;      // [P][ld]
+    uint64_t ld4;        // ld / 4
+    uint64_t P;
+    const float* x;      // [ld], zero beyond nvoxel
+    const float* g;      // [P] normalised measurement
+    const float* rinv;   // [P] (lambda_i > h_l) ? 1 / lambda_i : 0
+    float* fit;          // [P]
+    float* w;            // [P]
+    double* f2part;      // [gridDim.x]
+    const IterState* st; // may be null
+    uint32_t nrg;        // number of row groups = ceil(P / R)
+    int log_mode;
+};
+
+template <int R, int NT, int UNROLL>
+__global__ void __launch_bounds__(NT, 2) fp_rows_kernel(const FpArgs a) {
+    if (a.st && a.st->done) return;
+    constexpr int NW = NT / 32;
+    __shared__ double red[R][NW];
+    __shared__ double f2s[R];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float4* __restrict__ H4 = reinterpret_cast<const float4*>(a.H);
+    const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x);
+    const uint32_t ld4 = (uint32_t)a.ld4;
+    double f2acc = 0.0;
+
+    for (uint32_t rg = blockIdx.x; rg < a.nrg; rg += gridDim.x) {
+        const uint64_t row0 = (uint64_t)rg * R;
+        const int nvalid = (int)min((uint64_t)R, a.P - row0);
+        const float4* __restrict__ base = H4 + row0 * a.ld4;
+        uint32_t roff[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) roff[r] = (r < nvalid ? r : 0) * ld4;  // rows past the end re-read row0, result unused
+
+        float acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.f;
+
+        uint32_t c = tid;
+        for (; c + (UNROLL - 1) * NT < ld4; c += UNROLL * NT) {
+            float4 xv[UNROLL];
+            float4 h[UNROLL][R];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) xv[u] = __ldg(x4 + c + u * NT);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+                for (int r = 0; r < R; ++r) h[u][r] = ldg_stream(base + roff[r] + c + u * NT);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    acc[r] = fmaf(h[u][r].x, xv[u].x, acc[r]);
+                    acc[r] = fmaf(h[u][r].y, xv[u].y, acc[r]);
+                    acc[r] = fmaf(h[u][r].z, xv[u].z, acc[r]);
+                    acc[r] = fmaf(h[u][r].w, xv[u].w, acc[r]);
+                }
+        }
+        for (; c < ld4; c += NT) {
+            const float4 xv = __ldg(x4 + c);
+            float4 h[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) h[r] = ldg_stream(base + roff[r] + c);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                acc[r] = fmaf(h[r].x, xv.x, acc[r]);
+                acc[r] = fmaf(h[r].y, xv.y, acc[r]);
+                acc[r] = fmaf(h[r].z, xv.z, acc[r]);
+                acc[r] = fmaf(h[r].w, xv.w, acc[r]);
+            }
+        }
+
+        // cross-thread sums in fp64, fixed order
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const double s = warp_sum((double)acc[r]);
+            if (lane == 0) red[r][warp] = s;
+        }
+        __syncthreads();
+        if (tid < nvalid) {
+            double s = 0.0;
+#pragma unroll
+            for (int k = 0; k < NW; ++k) s += red[tid][k];
+            const uint64_t i = row0 + tid;
+            const float fitv = (float)s;
+            f2acc += s * s;
+            const float gi = a.g[i];
+            const float ri = a.rinv[i];
+            a.fit[i] = fitv;
+            float wi = 0.f;
+            if (gi >= 0.f) wi = a.log_mode ? fitv * ri : (gi - fitv) * ri;
+            a.w[i] = wi;
+        }
+        __syncthreads();
+    }
+
+    if (tid < R) f2s[tid] = f2acc;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) s += f2s[r];
+        a.f2part[blockIdx.x] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Back projection: s_j = sum_i H_ij w_i over the rows of one slab  (the main loop of PropagateKernel,
+// sart_kernels.cu:86-101, of InitialGuessKernel :40-54 and of LogPropagateKernel :146-170; CPU twins
+// sartsolver.cpp:149-157, 191-200, 295-310). grid = (column panels of NT float4, row slabs). A thread owns four
+// adjacent columns, walks down its slab with U rows in flight; the 32 row weights of a step are loaded once per
+// warp and broadcast by shuffle. Each (slab, column) partial is written exactly once: no atomics, no memset,
+// bit-reproducible. The slabs are added in fixed order by reduce_partials_kernel.
+// ---------------------------------------------------------------------------------------------------------------------
+struct BpArgs {
+    const float* H;
+    uint64_t ld4;
+    uint64_t P;
+    const float* w;          // [P]
+    float* part;             // [nslabs][ld]
+    uint32_t rows_per_slab;
+    const IterState* st;     // may be null
+};
+
+template <int NT, int U>
+__device__ __forceinline__ void bp_cols_body(const BpArgs& a, float* __restrict__ part) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint64_t c4 = (uint64_t)blockIdx.x * NT + tid;
+    const bool active = c4 < a.ld4;
+    const float4* __restrict__ base = reinterpret_cast<const float4*>(a.H) + (active ? c4 : a.ld4 - 1);
+    const uint64_t r0 = (uint64_t)blockIdx.y * a.rows_per_slab;
+    const uint64_t r1 = min(a.P, r0 + a.rows_per_slab);
+
+    float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0;
+    for (uint64_t r = r0; r < r1; r += 32) {
+        const uint64_t rl = r + lane;
+        const float wl = (rl < r1) ? __ldg(a.w + rl) : 0.f;
+        const float4* __restrict__ p = base + r * a.ld4;
+        if (r + 32 <= r1) {
+#pragma unroll
+            for (int k = 0; k < 32; k += U) {
+                float4 h[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) h[u] = ldg_stream(p + (uint64_t)(k + u) * a.ld4);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const float wv = __shfl_sync(FULL_MASK, wl, k + u);
+                    float4& acc = (u & 1) ? acc1 : acc0;
+                    acc.x = fmaf(h[u].x, wv, acc.x);
+                    acc.y = fmaf(h[u].y, wv, acc.y);
+                    acc.z = fmaf(h[u].z, wv, acc.z);
+                    acc.w = fmaf(h[u].w, wv, acc.w);
+                }
+            }
+        } else {
+            const int n = (int)(r1 - r);
+            for (int k = 0; k < n; ++k) {
+                const float4 h = ldg_stream(p + (uint64_t)k * a.ld4);
+                const float wv = __shfl_sync(FULL_MASK, wl, k);
+                acc0.x = fmaf(h.x, wv, acc0.x);
+                acc0.y = fmaf(h.y, wv, acc0.y);
+                acc0.z = fmaf(h.z, wv, acc0.z);
+                acc0.w = fmaf(h.w, wv, acc0.w);
+            }
+        }
+    }
+    if (active) {
+        float4 o;
+        o.x = acc0.x + acc1.x;
+        o.y = acc0.y + acc1.y;
+        o.z = acc0.z + acc1.z;
+        o.w = acc0.w + acc1.w;
+        reinterpret_cast<float4*>(part)[(uint64_t)blockIdx.y * a.ld4 + c4] = o;
+    }
+}
+
+template <int NT, int U>
+__global__ void __launch_bounds__(NT) bp_cols_kernel(const BpArgs a) {
+    if (a.st && a.st->done) return;
+    bp_cols_body<NT, U>(a, a.part);
+}
+
+// s_j = sum over slabs (fixed order, fp64) -> sred[j]
+__global__ void reduce_partials_kernel(const float* __restrict__ part, uint32_t nslabs, uint64_t ld, uint64_t V,
+                                       double* __restrict__ sred, const IterState* st) {
+    if (st && st->done) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    double s = 0.0;
+    for (uint32_t k = 0; k < nslabs; ++k) s += (double)part[(uint64_t)k * ld + j];
+    sred[j] = s;
+}
+
+// sum(fit^2) of this shard from the forward projection's per-CTA partials (one warp, fixed order); only launched
+// when several ranks have to all-reduce the scalar before the decision.
+__global__ void f2_sum_kernel(const double* __restrict__ f2part, uint32_t n, double* __restrict__ out, const IterState* st) {
+    if (st && st->done) return;
+    double f = 0.0;
+    for (uint32_t k = threadIdx.x; k < n; k += 32) f += f2part[k];
+    f = warp_sum(f);
+    if (threadIdx.x == 0) *out = f;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Decision for the iterate x_t the forward projection just evaluated (the host-side test of the reference,
+// sartsolver_cuda.cpp:251-261, CPU twin sartsolver.cpp:222-228), taken on the device BEFORE the back projection so
+// that a converged solve does not pay for one more matrix sweep. One warp. Reads state[t & 1], writes
+// state[(t + 1) & 1]; every later kernel of the sweep (and all later sweeps) looks at the new state.
+// ---------------------------------------------------------------------------------------------------------------------
+struct DecideArgs {
+    const double* f2part;  // per-CTA partials of sum(fit^2), or the all-reduced scalar (n == 1)
+    uint32_t n;
+    const FrameScalars* fs;
+    const IterState* st_in;
+    IterState* st_out;
+    double tol;
+    int max_iter, fixed, t;
+};
+
+__global__ void decide_kernel(const DecideArgs a) {
+    const IterState s = *a.st_in;
+    if (s.done) {
+        if (threadIdx.x == 0) *a.st_out = s;
+        return;
+    }
+    double f2 = 0.0;
+    for (uint32_t k = threadIdx.x; k < a.n; k += 32) f2 += a.f2part[k];
+    f2 = warp_sum(f2);
+    if (threadIdx.x != 0) return;
+    IterState o = s;
+    bool stop = false;
+    if (a.t >= 1) {
+        // sweep t evaluated x_t, the result of reference iteration iter = t - 1
+        const double m2 = a.fs->m2;
+        const double conv = (m2 - f2) / m2;
+        const int iter = a.t - 1;
+        if (!a.fixed && iter >= 1 && fabs(conv - s.conv_prev) < a.tol) {
+            stop = true;
+            o.status = 0;
+        } else if (a.t >= a.max_iter) {
+            stop = true;
+            o.status = -1;
+        }
+        o.conv_prev = conv;
+    }
+    if (stop) {
+        o.done = 1;
+        o.iterations = a.t;
+        o.final_buf = a.t & 1;
+    } else {
+        o.k = a.t + 1;
+    }
+    *a.st_out = o;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Update: x_{t+1} from x_t and the (all-reduced) back projection.
+// Replaces GradPenaltyKernel (sart_kernels.cu:179-189), the epilogue of PropagateKernel (:103-109) and
+// UpdateSolutionKernel (:205-212) / UpdateLogSolutionKernel (:215-224); CPU twins sartsolver.cpp:183-189, 201-209
+// and :287-293, 314-316. The Laplacian is CSR (rows sorted by column: the order the reference's sorted COO adds in);
+// the penalty uses the iterate BEFORE the update, which lives in the other buffer.
+// ---------------------------------------------------------------------------------------------------------------------
+struct UpdArgs {
+    const double* sred;         // [V] back-projected sums, already reduced over ranks
+    const double* xd_cur;       // [V] current iterate (normalised by norm), fp64 master copy
+    double* xd_next;            // [V]
+    float* xf_next;             // [ld] fp32 copy the next forward projection reads
+    const double* ray_density;  // [V]
+    const double* obs;          // [V] log solver: back-projected measurement (iteration-invariant)
+    const int* lap_rowptr;      // [V + 1] or null
+    const int* lap_col;
+    const float* lap_val;
+    const FrameScalars* fs;
+    const IterState* st;        // state after this sweep's decision
+    uint64_t V;
+    double beta, relax, h_d;
+    double eps_norm, eps_orig;  // log solver's epsilon: in normalised units (GPU semantics) or caller units (CPU, 1e-100)
+    int log_mode;
+};
+
+__global__ void update_kernel(const UpdArgs a) {
+    if (a.st->done) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= a.V) return;
+
+    double pen = 0.0;
+    if (a.lap_rowptr) {
+        const int b = a.lap_rowptr[j], e = a.lap_rowptr[j + 1];
+        for (int k = b; k < e; ++k) {
+            const double xv = a.xd_cur[a.lap_col[k]];
+            pen += a.beta * (double)a.lap_val[k] * (a.log_mode ? log(xv) : xv);
+        }
+    }
+    const double rho = a.ray_density[j];
+    const bool on = rho > a.h_d;
+    double xn;
+    if (!a.log_mode) {
+        const double diff = on ? a.sred[j] * (a.relax / rho) : 0.0;
+        xn = a.xd_cur[j] + (diff - pen);
+        if (signbit(xn)) xn = 0.0;
+    } else {
+        const double fitj = on ? a.sred[j] : 0.0;
+        const double eps = a.eps_norm + a.eps_orig / a.fs->norm;
+        xn = a.xd_cur[j] * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
+    }
+    a.xd_next[j] = xn;
+    a.xf_next[j] = (float)xn;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Per-frame prologue / epilogue (replaces pre_iteration_setup, sartsolver_cuda.cpp:138-194, and :264-265).
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void frame_stats_kernel(const double* __restrict__ g, uint64_t P, FrameScalars* fs) {
+    __shared__ double smax[32], ssum[32];
+    double mx = -INFINITY, sm = 0.0;
+    for (uint64_t i = threadIdx.x; i < P; i += blockDim.x) {
+        const double v = g[i];
+        mx = fmax(mx, v);
+        sm += (v > 0) ? v * v : 0.0;
+    }
+    mx = warp_max(mx);
+    sm = warp_sum(sm);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (lane == 0) {
+        smax[warp] = mx;
+        ssum[warp] = sm;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double m = smax[0], s = ssum[0];
+        for (int k = 1; k < nw; ++k) {
+            m = fmax(m, smax[k]);
+            s += ssum[k];
+        }
+        fs->gmax = m;
+        fs->gsq = s;
+    }
+}
+
+// weights_mode: 0 none, 1 initial guess CPU semantics (w = g), 2 initial guess GPU semantics (w = max(g, 0)),
+//               3 log solver's back-projected measurement (w = [g >= 0] g / lambda)
+__global__ void frame_prepare_kernel(const double* __restrict__ gd, uint64_t P, FrameScalars* fs,
+                                     const double* __restrict__ ray_length, double h_l, float* __restrict__ g,
+                                     float* __restrict__ rinv, float* __restrict__ w, int weights_mode) {
+    const double gmax = fs->gmax;
+    const double norm = (gmax > 0) ? gmax : 1.0;
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        fs->norm = norm;
+        fs->m2 = fs->gsq / (norm * norm);
+    }
+    if (i >= P) return;
+    const float gi = (float)(gd[i] / norm);
+    const double lam = ray_length[i];
+    const float ri = (lam > h_l) ? (float)(1.0 / lam) : 0.f;
+    g[i] = gi;
+    rinv[i] = ri;
+    if (weights_mode == 1) w[i] = gi;
+    else if (weights_mode == 2) w[i] = (gi > 0.f) ? gi : 0.f;
+    else if (weights_mode == 3) w[i] = (gi >= 0.f) ? gi * ri : 0.f;
+}
+
+// Starting solution. from_guess: x = caller's solution / norm (sartsolver_cuda.cpp:176-178); else the default
+// initial guess x_j = [rho_j > h_d] s_j / rho_j from the back-projected measurement (Eq. 4; sartsolver.cpp:149-157).
+// The lower clamp of the solver, if any, is max(floor_norm, floor_orig / norm): GPU semantics 1e-7 in normalised
+// units (sartsolver_cuda.cpp:180), CPU log solver 1e-100 in the caller's units (sartsolver.cpp:263).
+__global__ void start_solution_kernel(const double* __restrict__ sred, const double* __restrict__ xio,
+                                      const double* __restrict__ ray_density, double h_d, const FrameScalars* fs,
+                                      double floor_norm, double floor_orig, int from_guess, double* __restrict__ xd,
+                                      float* __restrict__ xf, uint64_t V) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    double x;
+    if (from_guess) x = xio[j] / fs->norm;
+    else {
+        const double rho = ray_density[j];
+        x = (rho > h_d) ? sred[j] / rho : 0.0;
+    }
+    const double floor_value = fmax(floor_norm, floor_orig / fs->norm);
+    if (floor_value > 0 && x < floor_value) x = floor_value;
+    xd[j] = x;
+    xf[j] = (float)x;
+}
+
+__global__ void mask_obs_kernel(const double* __restrict__ sred, const double* __restrict__ ray_density, double h_d,
+                                double* __restrict__ obs, uint64_t V) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < V) obs[j] = (ray_density[j] > h_d) ? sred[j] : 0.0;
+}
+
+__global__ void init_state_kernel(IterState* st0, IterState* st1) {
+    IterState s;
+    s.conv_prev = 0.0;
+    s.k = 0;
+    s.done = 0;
+    s.status = -1;
+    s.iterations = 0;
+    s.final_buf = 0;
+    s.pad = 0;
+    *st0 = s;
+    *st1 = s;
+}
+
+// xio_j = norm * x_final_j (sartsolver_cuda.cpp:264-265)
+__global__ void finish_solution_kernel(const double* __restrict__ xd0, const double* __restrict__ xd1,
+                                       const IterState* st, const FrameScalars* fs, double* __restrict__ xio,
+                                       uint64_t V) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    const double* src = st->final_buf ? xd1 : xd0;
+    xio[j] = fs->norm * src[j];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Once-per-matrix sums in fp64 (replaces the two host loops of the base constructor, sartsolver.cpp:38-56) and the
+// fp64 forward projection used to synthesise frames. Not on the per-iteration path.
+// ---------------------------------------------------------------------------------------------------------------------
+// out_i = sum_j H_ij * (x ? x_j : 1), one warp per row
+__global__ void forward_f64_kernel(const float* __restrict__ H, uint64_t ld4, uint64_t P, uint64_t V,
+                                   const double* __restrict__ x, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const uint64_t row = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= P) return;
+    const float4* __restrict__ p = reinterpret_cast<const float4*>(H) + row * ld4;
+    double acc = 0.0;
+    for (uint64_t c = lane; c < ld4; c += 32) {
+        const float4 h = ldg_stream(p + c);
+        const uint64_t j = 4 * c;
+        if (x) {
+            // columns past nvoxel hold zeros in H; x is only nvoxel long
+            acc += (double)h.x * (j + 0 < V ? x[j + 0] : 0.0);
+            acc += (double)h.y * (j + 1 < V ? x[j + 1] : 0.0);
+            acc += (double)h.z * (j + 2 < V ? x[j + 2] : 0.0);
+            acc += (double)h.w * (j + 3 < V ? x[j + 3] : 0.0);
+        } else {
+            acc += (double)h.x + (double)h.y + (double)h.z + (double)h.w;
+        }
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[row] = acc;
+}
+
+// part[slab][j] = sum over the slab's rows of H_ij, thread per column
+__global__ void col_sums_f64_kernel(const float* __restrict__ H, uint64_t ld, uint64_t P, uint64_t V,
+                                    uint32_t rows_per_slab, double* __restrict__ part) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    const uint64_t r0 = (uint64_t)blockIdx.y * rows_per_slab;
+    const uint64_t r1 = min(P, r0 + rows_per_slab);
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    const float* __restrict__ p = H + j;
+    uint64_t r = r0;
+    for (; r + 4 <= r1; r += 4) {
+        const float h0 = __ldg(p + (r + 0) * ld), h1 = __ldg(p + (r + 1) * ld);
+        const float h2 = __ldg(p + (r + 2) * ld), h3 = __ldg(p + (r + 3) * ld);
+        a0 += (double)h0;
+        a1 += (double)h1;
+        a2 += (double)h2;
+        a3 += (double)h3;
+    }
+    for (; r < r1; ++r) a0 += (double)__ldg(p + r * ld);
+    part[(uint64_t)blockIdx.y * V + j] = (a0 + a1) + (a2 + a3);
+}
+
+__global__ void reduce_f64_partials_kernel(const double* __restrict__ part, uint32_t nslabs, uint64_t V,
+                                           double* __restrict__ out) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    double s = 0.0;
+    for (uint32_t k = 0; k < nslabs; ++k) s += part[(uint64_t)k * V + j];
+    out[j] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Synthetic ray-transfer matrix: one splitmix64 draw per element keyed by the GLOBAL flattened index, an exact
+// integer < 2^24 scaled by one power of two (bit-identical on any rank count and to the CPU generator the tests use).
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t splitmix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+__device__ __forceinline__ float synth_element(uint64_t seed, uint64_t flat, float scale) {
+    const uint64_t h = splitmix64(seed ^ (flat * 0xD1342543DE82EF95ULL));
+    uint32_t q = (uint32_t)(h >> 48) | 1u;
+    if ((h & 63u) == 0) q += (uint32_t)((h >> 6) & 0x7FFFFFu);
+    return (float)q * scale;
+}
+
+__global__ void fill_synthetic_kernel(float* __restrict__ H, uint64_t ld4, uint64_t P, uint64_t V, uint64_t row_offset,
+                                      uint64_t seed, float scale) {
+    for (uint64_t row = blockIdx.y; row < P; row += gridDim.y) {
+        const uint64_t flat0 = (row_offset + row) * V;
+        float4* __restrict__ p = reinterpret_cast<float4*>(H) + row * ld4;
+        for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ld4; c += (uint64_t)gridDim.x * blockDim.x) {
+            const uint64_t j = 4 * c;
+            float4 v;
+            v.x = (j + 0 < V) ? synth_element(seed, flat0 + j + 0, scale) : 0.f;
+            v.y = (j + 1 < V) ? synth_element(seed, flat0 + j + 1, scale) : 0.f;
+            v.z = (j + 2 < V) ? synth_element(seed, flat0 + j + 2, scale) : 0.f;
+            v.w = (j + 3 < V) ? synth_element(seed, flat0 + j + 3, scale) : 0.f;
+            p[c] = v;
+        }
+    }
+}
+
+}  // namespace sart
