@@ -167,6 +167,15 @@ int sart_fetch_solution(sart_engine* e, double* solution);
  * accumulation on the device (what a camera would measure for emission x). */
 int sart_forward_project(sart_engine* e, const double* x, double* out);
 
+/* The two production sweep kernels on their own, for known-answer tests of the kernels (no reference counterpart as
+ * entry points; the arithmetic is cublasSgemv's, source/sartsolver_cuda.cpp:248-249, and the main loop of
+ * PropagateKernel, source/cuda/sart_kernels.cu:86-101):
+ *   sart_kernel_forward   fit[i] = sum_j H[i][j] * (float)x[j]     over the local rows (fp32 kernel, fp64 host I/O)
+ *   sart_kernel_backward  s[j]   = sum_i H[i][j] * (float)w[i]     over the local rows, NOT reduced over ranks
+ * They use the engine's per-solve work buffers: do not interleave them with a solve on another thread. */
+int sart_kernel_forward(sart_engine* e, const double* x, double* fit);
+int sart_kernel_backward(sart_engine* e, const double* w, double* s);
+
 int sart_get_stats(const sart_engine* e, sart_stats* out);
 
 #ifdef __cplusplus

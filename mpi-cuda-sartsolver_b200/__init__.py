@@ -28,6 +28,7 @@ SYMBOLS = [
     "sart_set_ray_length_threshold", "sart_set_convolution_tolerance", "sart_set_beta_laplace", "sart_set_relaxation",
     "sart_set_max_iterations", "sart_set_fixed_iterations", "sart_get_config", "sart_solve", "sart_stage_measurement",
     "sart_stage_guess", "sart_solve_resident", "sart_fetch_solution", "sart_forward_project", "sart_get_stats",
+    "sart_kernel_forward", "sart_kernel_backward",
 ]
 
 
@@ -103,6 +104,8 @@ def lib():
         L.sart_fetch_solution.argtypes = [_vp, _vp]
         L.sart_forward_project.argtypes = [_vp, _vp, _vp]
         L.sart_get_stats.argtypes = [_vp, C.POINTER(Stats)]
+        L.sart_kernel_forward.argtypes = [_vp, _vp, _vp]
+        L.sart_kernel_backward.argtypes = [_vp, _vp, _vp]
         for name in SYMBOLS:
             if name != "sart_last_error":
                 getattr(L, name).restype = C.c_int
@@ -272,6 +275,18 @@ class Engine:
         x = _f64(x)
         out = np.empty(self.nrows)
         check(lib().sart_forward_project(self._h, x.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def kernel_forward(self, x):
+        x = _f64(x)
+        out = np.empty(self.nrows)
+        check(lib().sart_kernel_forward(self._h, x.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def kernel_backward(self, w):
+        w = _f64(w)
+        out = np.empty(self.nvoxel)
+        check(lib().sart_kernel_backward(self._h, w.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)))
         return out
 
     def stats(self):

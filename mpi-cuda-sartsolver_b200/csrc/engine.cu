@@ -898,6 +898,32 @@ int sart_forward_project(sart_engine* e, const double* x, double* out) {
     return SART_OK;
 }
 
+int sart_kernel_forward(sart_engine* e, const double* x, double* fit) {
+    SART_TRY(require(e, false));
+    if (!x || !fit) return fail(SART_ERR_INVALID_ARGUMENT, "x or fit is NULL");
+    std::vector<float> xf(e->ld, 0.f), out(e->P);
+    for (uint64_t j = 0; j < e->V; ++j) xf[j] = (float)x[j];
+    CUDA_TRY(cudaMemcpyAsync(e->d_xf[0], xf.data(), e->ld * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    SART_TRY(launch_fp(e, e->d_xf[0], nullptr));
+    CUDA_TRY(cudaMemcpyAsync(out.data(), e->d_fit, e->P * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    for (uint64_t i = 0; i < e->P; ++i) fit[i] = out[i];
+    return SART_OK;
+}
+
+int sart_kernel_backward(sart_engine* e, const double* w, double* s) {
+    SART_TRY(require(e, false));
+    if (!w || !s) return fail(SART_ERR_INVALID_ARGUMENT, "w or s is NULL");
+    std::vector<float> wf(e->P);
+    for (uint64_t i = 0; i < e->P; ++i) wf[i] = (float)w[i];
+    CUDA_TRY(cudaMemcpyAsync(e->d_w, wf.data(), e->P * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    SART_TRY(launch_bp(e, nullptr));
+    SART_TRY(launch_reduce(e, nullptr));
+    CUDA_TRY(cudaMemcpyAsync(s, e->d_sred, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    return SART_OK;
+}
+
 int sart_get_stats(const sart_engine* e, sart_stats* out) {
     if (!e || !out) return fail(SART_ERR_INVALID_ARGUMENT, "engine or out is NULL");
     *out = e->stats;

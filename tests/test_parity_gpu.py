@@ -241,3 +241,21 @@ def test_full_size_properties_config2(sart):
         eng.set_max_iterations(3)
         x5 = eng.solve(g, xs)[0]
         assert rel_l2(x5, xs) <= TOL
+
+
+@pytest.mark.parametrize("P,V", [(1000, 1024), (257, 1000), (4099, 77), (31, 33), (64, 50000)])
+def test_sweep_kernels_known_answers(P, V, sart):
+    """The two production kernels alone against fp64 numpy on odd shapes (rows not a multiple of the row group or of
+    the 32-row slab step, columns not a multiple of 4 / 32 / the 1024-column panel)."""
+    rng = np.random.default_rng(P * 131 + V)
+    H = rng.random((P, V), dtype=np.float32)
+    H[rng.random(P) < 0.05] = 0
+    x = rng.random(V)
+    w = rng.standard_normal(P)
+    with sart.Engine(P, V, device=0) as eng:
+        eng.upload_rows(H)
+        fit = eng.kernel_forward(x)
+        s = eng.kernel_backward(w)
+    H64 = H.astype(np.float64)
+    assert rel_l2(fit, H64 @ x.astype(np.float32).astype(np.float64)) < 2e-6
+    assert rel_l2(s, H64.T @ w.astype(np.float32).astype(np.float64)) < 2e-6
