@@ -176,6 +176,25 @@ int sart_forward_project(sart_engine* e, const double* x, double* out);
 int sart_kernel_forward(sart_engine* e, const double* x, double* fit);
 int sart_kernel_backward(sart_engine* e, const double* w, double* s);
 
+/* Back projection without any device allocation -- this entry point has no counterpart in the reference.
+ * For hosts that reserved all GPU memory for their own arena (acquisition loops with a fixed budget, frameworks on a
+ * caching allocator, capped partitions): there a library-side cudaMalloc can fail, and it stalls every stream of the
+ * device when it does not. Such a caller cannot create an engine (sart_create allocates); it passes its own DEVICE
+ * buffers and gets the same column reduction the engine's back projection performs:
+ *     d_out[j] = sum_i d_matrix[i * ld + j] * d_weights[i]      0 <= i < nrows, 0 <= j < ncols   (fp64 result)
+ * d_matrix: row-major fp32, 16-byte aligned, leading dimension ld floats, ld % 4 == 0, ld >= ncols (the padding
+ * columns are read and ignored); d_weights fp32 [nrows]; d_out fp64 [ncols]; cuda_stream: a cudaStream_t (NULL = default
+ * stream) on the CURRENT device, to which all three buffers must belong. The two launches are asynchronous on it.
+ * Scratch: a 16 MiB array built into the library, one per GPU, resident on every GPU that loads the library until
+ * exit. Limit: ld <= SART_NOALLOC_MAX_LD; larger is refused (SART_ERR_INVALID_ARGUMENT). The array is shared by all
+ * calls and keeps the previous call's contents -- nothing in it needs clearing, a call reads only what it wrote -- but
+ * calls that overlap on one GPU race on it: serialise them (one stream, or events). The first call on each device looks
+ * up the array's address; make that call before starting any stream capture. */
+#define SART_NOALLOC_SCRATCH_BYTES (16u << 20)
+#define SART_NOALLOC_MAX_LD (4u << 20)
+int sart_back_project_noalloc(const float* d_matrix, uint64_t nrows, uint64_t ncols, uint64_t ld,
+                              const float* d_weights, double* d_out, void* cuda_stream);
+
 int sart_get_stats(const sart_engine* e, sart_stats* out);
 
 #ifdef __cplusplus

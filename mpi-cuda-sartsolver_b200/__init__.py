@@ -28,7 +28,7 @@ SYMBOLS = [
     "sart_set_ray_length_threshold", "sart_set_convolution_tolerance", "sart_set_beta_laplace", "sart_set_relaxation",
     "sart_set_max_iterations", "sart_set_fixed_iterations", "sart_get_config", "sart_solve", "sart_stage_measurement",
     "sart_stage_guess", "sart_solve_resident", "sart_fetch_solution", "sart_forward_project", "sart_get_stats",
-    "sart_kernel_forward", "sart_kernel_backward",
+    "sart_kernel_forward", "sart_kernel_backward", "sart_back_project_noalloc",
 ]
 
 
@@ -106,6 +106,7 @@ def lib():
         L.sart_get_stats.argtypes = [_vp, C.POINTER(Stats)]
         L.sart_kernel_forward.argtypes = [_vp, _vp, _vp]
         L.sart_kernel_backward.argtypes = [_vp, _vp, _vp]
+        L.sart_back_project_noalloc.argtypes = [_vp, _u64, _u64, _u64, _vp, _vp, _vp]
         for name in SYMBOLS:
             if name != "sart_last_error":
                 getattr(L, name).restype = C.c_int
@@ -142,6 +143,15 @@ def comm_unique_id():
     buf = (C.c_uint8 * UNIQUE_ID_BYTES)()
     check(lib().sart_comm_unique_id(buf))
     return bytes(buf)
+
+
+NOALLOC_MAX_LD = 4 << 20
+
+
+def back_project_noalloc(d_matrix, nrows, ncols, ld, d_weights, d_out, stream=None):
+    """sart_back_project_noalloc on raw DEVICE addresses (ints): for callers whose GPU memory is entirely theirs and
+    who therefore cannot let a library allocate. Asynchronous on ``stream`` (a cudaStream_t as int, None = default)."""
+    check(lib().sart_back_project_noalloc(d_matrix, nrows, ncols, ld, d_weights, d_out, stream))
 
 
 def _f64(a):

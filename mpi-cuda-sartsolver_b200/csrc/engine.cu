@@ -932,3 +932,101 @@ int sart_get_stats(const sart_engine* e, sart_stats* out) {
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// Back projection for callers that must not allocate device memory.
+//
+// Who that is: hosts that gave the whole GPU to their own arena at start-up -- a data-acquisition loop that sized every
+// buffer up front, a framework sitting on a caching allocator, a partition with a hard memory cap -- and that call the
+// back projection from inside that loop. There, a cudaMalloc inside a library can fail outright (nothing is left outside
+// the arena) and, when it succeeds, it serialises the whole device, which shows up as a hitch in every other stream of
+// the loop. sart_create() allocates, so such callers cannot use an engine; they own the matrix, the weights and the
+// output themselves and only need the kernel.
+//
+// The slab partials that bp_cols_kernel keeps in a cudaMalloc'ed buffer live here in a fixed array inside the library
+// image instead. Consequences a caller has to know:
+//   * The array costs SART_NOALLOC_SCRATCH_BYTES (16 MiB) on every GPU that loads the library, until the process exits.
+//   * It bounds the problem: the padded row length ld may not exceed SART_NOALLOC_MAX_LD floats; anything larger is
+//     refused with SART_ERR_INVALID_ARGUMENT, nothing is launched.
+//   * It is ONE array per GPU, shared by every call and never cleared. No element has to start at zero: the reduction
+//     reads only the slabs x ld partials that the first kernel of the same call has just written, and stale values
+//     from an earlier call beyond that range are never read. Two calls that overlap on the same GPU (different streams
+//     or host threads without ordering between them) write the same partials and race; order them yourself.
+//   * The first call on each device looks the array's device address up (cudaGetSymbolAddress with that device
+//     current; the name of a __device__ array is only a host-side handle and must never be handed to a kernel). That
+//     first call may make the runtime load the module, so make it before any stream capture begins.
+// The function calls no cudaMalloc / cudaFree / cudaMallocAsync and no library routine that allocates on the device.
+// =====================================================================================================================
+#define SART_NOALLOC_SCRATCH_FLOATS (4u << 20)
+
+static __device__ __align__(256) float g_noalloc_scratch[SART_NOALLOC_SCRATCH_FLOATS];
+
+namespace {
+
+constexpr int kNoallocMaxDevices = 64;
+float* g_noalloc_ptr[kNoallocMaxDevices];  // device address of g_noalloc_scratch on each device, null until looked up
+int g_noalloc_sms[kNoallocMaxDevices];
+std::mutex g_noalloc_mutex;
+
+// bp_cols_kernel with its partials in the library's own array (address passed in: see the note on the first call)
+template <int NT, int U>
+__global__ void __launch_bounds__(NT) bp_cols_scratch_kernel(const BpArgs a, float* scratch) {
+    bp_cols_body<NT, U>(a, scratch);
+}
+
+}  // namespace
+
+extern "C" int sart_back_project_noalloc(const float* d_matrix, uint64_t nrows, uint64_t ncols, uint64_t ld,
+                                         const float* d_weights, double* d_out, void* cuda_stream) {
+    if (!d_matrix || !d_weights || !d_out) return fail(SART_ERR_INVALID_ARGUMENT, "sart_back_project_noalloc: NULL device pointer");
+    if (nrows == 0 || ncols == 0 || ld < ncols || ld % 4 != 0 || (reinterpret_cast<uintptr_t>(d_matrix) & 15))
+        return fail(SART_ERR_INVALID_ARGUMENT,
+                    "sart_back_project_noalloc: need nrows, ncols > 0, ld >= ncols, ld a multiple of 4 floats and a 16-byte aligned matrix");
+    if (ld > SART_NOALLOC_SCRATCH_FLOATS)
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_back_project_noalloc: row length ld = " + std::to_string(ld) +
+                                                   " floats exceeds the built-in scratch (at most " +
+                                                   std::to_string(SART_NOALLOC_SCRATCH_FLOATS) +
+                                                   "); use an engine (sart_create) for wider matrices");
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoallocMaxDevices) return fail(SART_ERR_INVALID_ARGUMENT, "sart_back_project_noalloc: device ordinal too large");
+    float* scratch = nullptr;
+    int sms = 0;
+    {
+        std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+        if (!g_noalloc_ptr[dev]) {  // first call on this device, which is the current one
+            float* ptr = nullptr;
+            CUDA_TRY(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+            CUDA_TRY(cudaDeviceGetAttribute(&g_noalloc_sms[dev], cudaDevAttrMultiProcessorCount, dev));
+            g_noalloc_ptr[dev] = ptr;
+        }
+        scratch = g_noalloc_ptr[dev];
+        sms = g_noalloc_sms[dev];
+    }
+
+    // one wave of (1024-column panels) x (row slabs of a multiple of 32 rows), as many slabs as the array can hold
+    const uint64_t ld4 = ld / 4;
+    const uint64_t panels = ceil_div(ld4, kBpThreads);
+    uint64_t slabs = std::max<uint64_t>(1, (uint64_t)sms * 4 / panels);
+    slabs = std::min<uint64_t>(slabs, SART_NOALLOC_SCRATCH_FLOATS / ld);
+    slabs = std::min<uint64_t>(slabs, ceil_div(nrows, 32));
+    const uint64_t rows_per_slab = ceil_div(ceil_div(nrows, slabs), 32) * 32;
+    slabs = ceil_div(nrows, rows_per_slab);
+    if (panels > 0x7fffffffULL || slabs > 65535 || rows_per_slab > 0xffffffffULL)
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_back_project_noalloc: problem too large for one launch");
+
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+    BpArgs a;
+    a.H = d_matrix;
+    a.ld4 = ld4;
+    a.P = nrows;
+    a.w = d_weights;
+    a.part = nullptr;
+    a.rows_per_slab = (uint32_t)rows_per_slab;
+    a.st = nullptr;
+    bp_cols_scratch_kernel<kBpThreads, 8><<<dim3((uint32_t)panels, (uint32_t)slabs), kBpThreads, 0, stream>>>(a, scratch);
+    CUDA_TRY(cudaGetLastError());
+    reduce_partials_kernel<<<(uint32_t)ceil_div(ncols, 256), 256, 0, stream>>>(scratch, (uint32_t)slabs, ld, ncols, d_out, nullptr);
+    CUDA_TRY(cudaGetLastError());
+    return SART_OK;
+}
