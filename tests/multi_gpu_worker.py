@@ -1,0 +1,78 @@
+"""Worker for the multi-GPU parity test: run under torchrun, one rank per GPU.
+
+Every rank owns its row shard (source/main.cpp:67-68), feeds its slice of each frame, and must end with the same
+full-length solution as the CPU oracle. Rank 0 alone is given the Laplacian, as in the reference (source/main.cpp:73-74)."""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import load_package  # noqa: E402
+from bench import load_module  # noqa: E402
+from oracle.pyoracle import Restatement  # noqa: E402
+from tests.cases import load_synthetic, rel_l2  # noqa: E402
+
+
+def main():
+    sart = load_package()
+    cpl = load_module("control_plane")
+    cp = cpl.ControlPlane.from_env(timeout_s=300)
+    syn = load_synthetic()
+    res = Restatement()
+    out = {"rank": cp.rank, "world": cp.world, "checks": {}}
+    uid = cp.broadcast_bytes(sart.comm_unique_id() if cp.rank == 0 else None)
+
+    def make_engine(P, V, **kw):
+        eng = sart.Engine(P, V, rank=cp.rank, nranks=cp.world, device=cp.local_rank, **kw)
+        return eng
+
+    first = True
+    for name, P, V, kw, use_lap, saturated in [
+        ("linear_fixed", 1030, 515, dict(max_iterations=20, fixed_iterations=True), True, False),
+        ("linear_tol", 777, 300, dict(max_iterations=400, conv_tolerance=1e-4), False, True),
+        ("log_fixed", 900, 256, dict(max_iterations=15, fixed_iterations=True, logarithmic=True, relaxation=0.7), True, False),
+    ]:
+        H = res.fill_synthetic(P, V, 31)
+        g = res.forward(H, syn.emission_profile(V))
+        if saturated:
+            g[::13] = -1.0
+        lap = syn.laplacian_coo(V) if use_lap else None
+        okw = dict(kw)
+        x_ref, st_ref, it_ref = res.solve(H, g, lap=lap, beta_laplace=2e-2, nranks=cp.world, **okw)
+        eng = make_engine(P, V, beta_laplace=2e-2, **kw)
+        # NCCL allows one communicator per engine; every engine of this worker needs its own id
+        if not first:
+            uid = cp.broadcast_bytes(sart.comm_unique_id() if cp.rank == 0 else None)
+        first = False
+        eng.comm_init(uid)
+        off, n = eng.row_offset, eng.nrows
+        eng.fill_synthetic(31)
+        np.testing.assert_array_equal(eng.download_rows(), H[off:off + n])
+        if lap is not None and cp.rank == 0:
+            eng.set_laplacian(*lap)
+        eng.finalize()
+        rho, lam = eng.ray_sums()
+        rho_ref, lam_ref = res.ray_sums(H, cp.world)
+        x, st, it = eng.solve(g[off:off + n])
+        # warm-started second frame
+        x2, st2, it2 = eng.solve(1.1 * g[off:off + n], x)
+        x2_ref, st2_ref, it2_ref = res.solve(H, 1.1 * g, x0=x_ref, lap=lap, beta_laplace=2e-2, nranks=cp.world, **okw)
+        eng.close()
+        out["checks"][name] = {
+            "rho": rel_l2(rho, rho_ref), "lam": rel_l2(lam, lam_ref[off:off + n]),
+            "x": rel_l2(x, x_ref), "status": [st, st_ref], "iterations": [it, it_ref],
+            "x2": rel_l2(x2, x2_ref), "iterations2": [it2, it2_ref],
+            "x_hash": float(np.sum(x * np.arange(1, V + 1))),
+        }
+    gathered = cp.gather(out)
+    cp.barrier()
+    cp.shutdown()
+    if cp.rank == 0:
+        print("RESULT " + json.dumps(gathered))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,47 @@
+"""Row-sharded solve on several GPUs of one box (one process per GPU, NCCL all-reduce between the engines) against the
+CPU oracle run with the same rank split. Skipped on single-GPU boxes; run it with `gpurun --gpus 2`."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_solve_matches_oracle(world):
+    if _gpu_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_worker.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-4000:]
+    line = [l for l in out.stdout.splitlines() if l.startswith("RESULT ")][0]
+    ranks = json.loads(line[7:])
+    assert len(ranks) == world
+    for name in ranks[0]["checks"]:
+        hashes = set()
+        for r in ranks:
+            c = r["checks"][name]
+            assert c["rho"] < 1e-13 and c["lam"] < 1e-13, (name, c)
+            assert c["status"][0] == c["status"][1], (name, c)
+            assert abs(c["iterations"][0] - c["iterations"][1]) <= 1, (name, c)
+            if c["iterations"][0] == c["iterations"][1]:
+                assert c["x"] <= 1e-5, (name, c)
+            if c["iterations2"][0] == c["iterations2"][1]:
+                assert c["x2"] <= 1e-5, (name, c)
+            hashes.add(c["x_hash"])
+        assert len(hashes) == 1, f"{name}: ranks ended with different solutions"
