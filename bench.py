@@ -63,7 +63,7 @@ def profiled_traffic(kernel):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms; only samples inside the timed region count."""
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
@@ -74,7 +74,7 @@ class ClockSampler:
         if exe:
             try:
                 self.proc = subprocess.Popen([exe, "-i", str(device), "--query-gpu=" + self.FIELDS,
-                                              "--format=csv,noheader,nounits", "-lms", "200"],
+                                              "--format=csv,noheader,nounits", "-lms", "50"],
                                              stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
                 self.thread = threading.Thread(target=self._pump, daemon=True)
                 self.thread.start()
@@ -95,7 +95,7 @@ class ClockSampler:
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for t, line in self.rows:
-            if not (t0 - 0.2 <= t <= t1 + 0.2):
+            if not (t0 - 0.05 <= t <= t1 + 0.05):
                 continue
             f = [x.strip() for x in line.split(",")]
             try:
@@ -222,9 +222,9 @@ def run_engine_arm(args, cp):
     # ---- value: inputs resident in HBM -------------------------------------------------------------------------------
     eng.stage_measurement(g)
     eng.stage_guess(guess)
+    sampler = ClockSampler(device) if cp.rank == 0 else None  # started before the warm-up so samples flow by t0
     for _ in range(args.warmup):
         resident_step()
-    sampler = ClockSampler(device) if cp.rank == 0 else None
     cp.barrier()
     w0 = time.perf_counter()
     dev_ms, launches, fp_ms, bp_ms, fp_n, bp_n = 0.0, 0, 0.0, 0.0, 0, 0
