@@ -39,6 +39,14 @@ extern "C" {
 #define SART_SEMANTICS_CPU 0
 #define SART_SEMANTICS_GPU 1
 
+/* How one iteration passes over the matrix (no reference counterpart; results agree within the parity tolerance).
+ * SPLIT: forward projection and back projection as two kernels, two reads of the shard from HBM.
+ * FUSED: one cluster kernel that keeps each row in shared memory between its forward and back projection, one read
+ *        of the shard from HBM; needs nvoxel <= 245 760 (16 CTAs x 3840 float4 columns). AUTO picks FUSED for long rows. */
+#define SART_SWEEP_AUTO 0
+#define SART_SWEEP_SPLIT 1
+#define SART_SWEEP_FUSED 2
+
 #define SART_UNIQUE_ID_BYTES 128
 
 typedef struct sart_engine sart_engine;
@@ -55,7 +63,7 @@ typedef struct sart_config {
     int32_t semantics;        /* SART_SEMANTICS_* */
     int32_t max_iterations;   /* default 2000 */
     int32_t fixed_iterations; /* 1: never test convergence, always run max_iterations (benchmark switch; not in the reference) */
-    int32_t reserved;
+    int32_t sweep_mode;       /* SART_SWEEP_*: how an iteration passes over the matrix (default AUTO) */
     double ray_density_threshold; /* default 1e-6 */
     double ray_length_threshold;  /* default 1e-6 */
     double conv_tolerance;        /* default 1e-5 */
@@ -78,6 +86,9 @@ typedef struct sart_stats {
     uint64_t matrix_bytes;   /* npixel_local * nvoxel * 4: algorithmic bytes of ONE sweep of this shard */
     uint64_t h2d_bytes;      /* host->device bytes moved by the last solve */
     uint64_t d2h_bytes;      /* device->host bytes moved by the last solve */
+    double fused_ms_avg;     /* mean duration of one fused forward+back projection launch (SART_SWEEP_FUSED) */
+    int32_t fused_launches;  /* launches behind fused_ms_avg */
+    int32_t sweep_mode;      /* SART_SWEEP_SPLIT or SART_SWEEP_FUSED: what the engine runs */
 } sart_stats;
 
 typedef struct sart_device_info {

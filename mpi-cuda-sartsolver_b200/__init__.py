@@ -18,6 +18,7 @@ ERR_INVALID_ARGUMENT, ERR_CUDA, ERR_STATE, ERR_NCCL, ERR_NO_DEVICE = 1, 2, 3, 4,
 SUCCESS = 0
 MAX_ITERATIONS_EXCEEDED = -1
 SEMANTICS_CPU, SEMANTICS_GPU = 0, 1
+SWEEP_AUTO, SWEEP_SPLIT, SWEEP_FUSED = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
 # every symbol include/sart_b200.h declares (tests check the library exports exactly these)
@@ -37,7 +38,7 @@ class Config(C.Structure):
         ("npixel", C.c_uint64), ("nvoxel", C.c_uint64),
         ("rank", C.c_int32), ("nranks", C.c_int32), ("device", C.c_int32), ("logarithmic", C.c_int32),
         ("semantics", C.c_int32), ("max_iterations", C.c_int32), ("fixed_iterations", C.c_int32),
-        ("reserved", C.c_int32),
+        ("sweep_mode", C.c_int32),
         ("ray_density_threshold", C.c_double), ("ray_length_threshold", C.c_double), ("conv_tolerance", C.c_double),
         ("beta_laplace", C.c_double), ("relaxation", C.c_double),
     ]
@@ -49,6 +50,7 @@ class Stats(C.Structure):
         ("solve_ms", C.c_double), ("iterate_ms", C.c_double), ("fp_ms_avg", C.c_double), ("bp_ms_avg", C.c_double),
         ("fp_launches", C.c_int32), ("bp_launches", C.c_int32),
         ("matrix_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+        ("fused_ms_avg", C.c_double), ("fused_launches", C.c_int32), ("sweep_mode", C.c_int32),
     ]
 
 
@@ -163,11 +165,12 @@ class Engine:
 
     def __init__(self, npixel, nvoxel, rank=0, nranks=1, device=-1, logarithmic=False, semantics=SEMANTICS_CPU,
                  ray_density_threshold=1e-6, ray_length_threshold=1e-6, conv_tolerance=1e-5, beta_laplace=1e-2,
-                 relaxation=1.0, max_iterations=2000, fixed_iterations=False):
+                 relaxation=1.0, max_iterations=2000, fixed_iterations=False, sweep_mode=SWEEP_AUTO):
         self._h = C.c_void_p()
         cfg = default_config(npixel=npixel, nvoxel=nvoxel, rank=rank, nranks=nranks, device=device,
                              logarithmic=int(logarithmic), semantics=semantics, max_iterations=max_iterations,
-                             fixed_iterations=int(fixed_iterations), ray_density_threshold=ray_density_threshold,
+                             fixed_iterations=int(fixed_iterations), sweep_mode=sweep_mode,
+                             ray_density_threshold=ray_density_threshold,
                              ray_length_threshold=ray_length_threshold, conv_tolerance=conv_tolerance,
                              beta_laplace=beta_laplace, relaxation=relaxation)
         check(lib().sart_create(C.byref(cfg), C.byref(self._h)))

@@ -18,6 +18,7 @@
 
 #include "../../include/sart_b200.h"
 #include "kernels.cuh"
+#include "fused.cuh"
 #include "nccl_dyn.h"
 
 using namespace sart;
@@ -106,6 +107,11 @@ struct sart_engine {
     uint32_t fp_grid = 0, fp_nrg = 0;
     int fp_variant = 0, bp_variant = 0, fp_rows = 8;
     int batch = 1;
+    // fused sweep (cluster kernel): geometry, 0 clusters = not available for this shape / device
+    bool fused = false;
+    uint32_t fu_cluster = 0, fu_wc = 0, fu_stages = 0, fu_stage_bytes = 0, fu_smem = 0, fu_nclusters = 0;
+    void (*fu_kernel)(const sart::FusedArgs) = nullptr;
+    uint32_t fu_threads = 0;
 
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
     cudaEvent_t ev_batch[2] = {nullptr, nullptr};
@@ -196,6 +202,135 @@ int plan_launches(sart_engine* e) {
     return SART_OK;
 }
 
+typedef void (*FusedKernel)(const FusedArgs);
+
+// Consumer-thread counts the fused kernel is built for. One extra warp produces, and registers are handed out per
+// SM sub-partition (16 K each), so 15 + 1 warps leave 128 registers per thread and 7 + 1 warps leave 255.
+// K = float4 columns a consumer thread owns (its slice of x and of s lives in registers): the smallest K that covers
+// the panel is used.
+template <int NT, int KMAX>
+struct FusedFamily {
+    template <int K>
+    static FusedKernel pick(int k) {
+        if constexpr (K > KMAX) return nullptr;
+        else return (k <= K) ? fused_sweep_kernel<NT, K> : pick<K + 1>(k);
+    }
+};
+constexpr int kFusedThreadsWide = 480, kFusedKWide = 8;      // 16 warps, <= 128 registers
+constexpr int kFusedThreadsNarrow = 224, kFusedKNarrow = 16;  // 8 warps, <= 255 registers
+
+// Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
+// registers (<= K float4 per thread), as many shared-memory stages of one row panel as fit, and as many clusters as
+// the device can keep resident. Leaves e->fused false when the shape or the device cannot run it.
+int plan_fused(sart_engine* e) {
+    e->fused = false;
+    const int mode = e->cfg.sweep_mode;
+    if (mode == SART_SWEEP_SPLIT) return SART_OK;
+    const bool narrow = env_int("SART_FUSED_THREADS", kFusedThreadsWide) == kFusedThreadsNarrow;
+    const uint32_t nt = narrow ? kFusedThreadsNarrow : kFusedThreadsWide;
+    const uint64_t max_wc = (uint64_t)nt * (narrow ? kFusedKNarrow : kFusedKWide);
+    uint32_t C = 0;
+    for (uint32_t c : {1u, 2u, 4u, 8u, 16u})
+        if (ceil_div(e->ld4, c) <= max_wc) {
+            C = c;
+            break;
+        }
+    const int forced_c = env_int("SART_FUSED_CLUSTER", 0);
+    if (forced_c > 0 && ceil_div(e->ld4, (uint64_t)forced_c) <= max_wc) C = (uint32_t)forced_c;
+    auto unavailable = [&](const std::string& why) {
+        if (mode == SART_SWEEP_FUSED) return fail(SART_ERR_INVALID_ARGUMENT, "SART_SWEEP_FUSED is not available: " + why);
+        return (int)SART_OK;
+    };
+    if (!C) return unavailable("nvoxel exceeds what 16 CTAs can hold in registers");
+    const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
+    const uint32_t stage_bytes = (uint32_t)(ceil_div((uint64_t)wc * 16, 128) * 128);
+    const uint32_t nw = nt / 32;
+    int max_smem = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+    uint32_t S = 0, smem = 0;
+    const uint32_t s_cap = (uint32_t)std::max(2, env_int("SART_FUSED_STAGES", 8));
+    for (uint32_t s = s_cap; s >= 2; --s) {
+        const uint64_t need = (uint64_t)s * stage_bytes + (uint64_t)2 * s * C * nw * 4 + (uint64_t)4 * s * 8;
+        if (need <= (uint64_t)max_smem) {
+            S = s;
+            smem = (uint32_t)need;
+            break;
+        }
+    }
+    if (!S) return unavailable("a row panel does not fit twice into shared memory");
+    // long rows only, unless forced: short rows make the per-row exchange dominate
+    if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 2048)) return SART_OK;
+
+    const int k_need = (int)ceil_div(wc, nt);
+    const FusedKernel kFusedKernel = narrow ? FusedFamily<kFusedThreadsNarrow, kFusedKNarrow>::pick<1>(k_need)
+                                            : FusedFamily<kFusedThreadsWide, kFusedKWide>::pick<1>(k_need);
+    if (!kFusedKernel) return unavailable("no kernel instance for this panel width");
+    e->fu_kernel = kFusedKernel;
+    e->fu_threads = nt;
+    CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (C > 8) CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(C * (uint32_t)e->sm_count, 1, 1);
+    cfg.blockDim = dim3(nt + 32, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int nclusters = 0;
+    cudaError_t err = cudaOccupancyMaxActiveClusters(&nclusters, kFusedKernel, &cfg);
+    if (err != cudaSuccess || nclusters <= 0) {
+        (void)cudaGetLastError();
+        return unavailable(std::string("the device cannot co-schedule a cluster of ") + std::to_string(C) + " CTAs (" +
+                           (err != cudaSuccess ? cudaGetErrorString(err) : "0 active clusters") + ")");
+    }
+    const int forced_n = env_int("SART_FUSED_CLUSTERS", 0);
+    if (forced_n > 0) nclusters = std::min(nclusters, forced_n);
+    e->fu_cluster = C;
+    e->fu_wc = wc;
+    e->fu_stages = S;
+    e->fu_stage_bytes = stage_bytes;
+    e->fu_smem = smem;
+    e->fu_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
+    e->fused = true;
+    return SART_OK;
+}
+
+int launch_fused(sart_engine* e, const float* x, const IterState* st) {
+    FusedArgs a;
+    a.H = e->dH;
+    a.ld4 = e->ld4;
+    a.P = e->P;
+    a.x = x;
+    a.g = e->d_g;
+    a.rinv = e->d_rinv;
+    a.part = e->d_part;
+    a.f2part = e->d_f2part;
+    a.st = st;
+    a.Wc = e->fu_wc;
+    a.stages = e->fu_stages;
+    a.stage_bytes = e->fu_stage_bytes;
+    a.log_mode = e->cfg.logarithmic;
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = e->fu_cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(e->fu_cluster * e->fu_nclusters, 1, 1);
+    cfg.blockDim = dim3(e->fu_threads + 32, 1, 1);
+    cfg.dynamicSmemBytes = e->fu_smem;
+    cfg.stream = e->stream;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CUDA_TRY(cudaLaunchKernelEx(&cfg, e->fu_kernel, a));
+    ++e->launches;
+    return SART_OK;
+}
+
 int launch_fp(sart_engine* e, const float* x, const IterState* st) {
     FpArgs a;
     a.H = e->dH;
@@ -232,9 +367,9 @@ int launch_bp(sart_engine* e, const IterState* st) {
     return SART_OK;
 }
 
-int launch_reduce(sart_engine* e, const IterState* st) {
+int launch_reduce(sart_engine* e, const IterState* st, uint32_t nslabs = 0) {
     const uint32_t blocks = (uint32_t)ceil_div(e->V, 256);
-    reduce_partials_kernel<<<blocks, 256, 0, e->stream>>>(e->d_part, e->bp_slabs, e->ld, e->V, e->d_sred, st);
+    reduce_partials_kernel<<<blocks, 256, 0, e->stream>>>(e->d_part, nslabs ? nslabs : e->bp_slabs, e->ld, e->V, e->d_sred, st);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
@@ -251,44 +386,7 @@ int allreduce_f64(sart_engine* e, double* buf, uint64_t count, ncclRedOp_t op) {
 // One sweep for the iterate x_t: forward projection, decision, and -- unless t is the last possible sweep, where
 // the decision can only be "stop" -- back projection, reduction and update. Kernels after the decision test the
 // freshly written state, so nothing but the forward projection runs once the solve is over.
-int enqueue_sweep(sart_engine* e, int t) {
-    const IterState* st_in = e->d_st[t & 1];
-    IterState* st_out = e->d_st[(t + 1) & 1];
-    const bool prof = e->profiling && t < kProfiledSweeps;
-    const bool last = t >= e->cfg.max_iterations;
-    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
-    SART_TRY(launch_fp(e, e->d_xf[t & 1], st_in));
-    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
-
-    DecideArgs d;
-    d.f2part = e->d_f2part;
-    d.n = e->fp_grid;
-    if (e->cfg.nranks > 1) {
-        f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_f2part, e->fp_grid, e->d_f2, st_in);
-        CUDA_TRY(cudaGetLastError());
-        ++e->launches;
-        SART_TRY(allreduce_f64(e, e->d_f2, 1, ncclSum));
-        d.f2part = e->d_f2;
-        d.n = 1;
-    }
-    d.fs = e->d_fs;
-    d.st_in = st_in;
-    d.st_out = st_out;
-    d.tol = e->cfg.conv_tolerance;
-    d.max_iter = e->cfg.max_iterations;
-    d.fixed = e->cfg.fixed_iterations;
-    d.t = t;
-    decide_kernel<<<1, 32, 0, e->stream>>>(d);
-    CUDA_TRY(cudaGetLastError());
-    ++e->launches;
-    if (last) return SART_OK;
-
-    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
-    SART_TRY(launch_bp(e, st_out));
-    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
-    SART_TRY(launch_reduce(e, st_out));
-    SART_TRY(allreduce_f64(e, e->d_sred, e->V, ncclSum));
-
+int launch_update(sart_engine* e, int t, const IterState* st) {
     UpdArgs u;
     u.sred = e->d_sred;
     u.xd_cur = e->d_xd[t & 1];
@@ -300,7 +398,7 @@ int enqueue_sweep(sart_engine* e, int t) {
     u.lap_col = e->d_lap_col;
     u.lap_val = e->d_lap_val;
     u.fs = e->d_fs;
-    u.st = st_out;
+    u.st = st;
     u.V = e->V;
     u.beta = e->cfg.beta_laplace;
     u.relax = e->cfg.relaxation;
@@ -312,6 +410,80 @@ int enqueue_sweep(sart_engine* e, int t) {
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
+}
+
+int launch_decide(sart_engine* e, int t, const double* f2, uint32_t n, const IterState* st_in, IterState* st_out) {
+    DecideArgs d;
+    d.f2part = f2;
+    d.n = n;
+    d.fs = e->d_fs;
+    d.st_in = st_in;
+    d.st_out = st_out;
+    d.tol = e->cfg.conv_tolerance;
+    d.max_iter = e->cfg.max_iterations;
+    d.fixed = e->cfg.fixed_iterations;
+    d.t = t;
+    decide_kernel<<<1, 32, 0, e->stream>>>(d);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+// One sweep for the iterate x_t.
+// SPLIT: forward projection, decision, and -- unless t is the last possible sweep, where the decision can only be
+//   "stop" -- back projection, reduction and update; kernels after the decision test the freshly written state, so
+//   nothing but the forward projection runs once the solve is over.
+// FUSED: one cluster kernel does both projections from a single pass over HBM, then reduction (the scalar sum(fit^2)
+//   rides along in the same all-reduce), decision, update. The last possible sweep only needs sum(fit^2): it runs the
+//   plain forward projection.
+int enqueue_sweep(sart_engine* e, int t) {
+    const IterState* st_in = e->d_st[t & 1];
+    IterState* st_out = e->d_st[(t + 1) & 1];
+    const bool prof = e->profiling && t < kProfiledSweeps;
+    const bool last = t >= e->cfg.max_iterations;
+    const bool multi = e->cfg.nranks > 1;
+
+    if (e->fused && !last) {
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+        SART_TRY(launch_fused(e, e->d_xf[t & 1], st_in));
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        SART_TRY(launch_reduce(e, st_in, e->fu_nclusters));
+        const double* f2 = e->d_f2part;
+        uint32_t nf2 = e->fu_nclusters;
+        if (multi) {
+            f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_f2part, e->fu_nclusters, e->d_sred + e->V, st_in);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+            SART_TRY(allreduce_f64(e, e->d_sred, e->V + 1, ncclSum));
+            f2 = e->d_sred + e->V;
+            nf2 = 1;
+        }
+        SART_TRY(launch_decide(e, t, f2, nf2, st_in, st_out));
+        return launch_update(e, t, st_out);
+    }
+
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
+    SART_TRY(launch_fp(e, e->d_xf[t & 1], st_in));
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
+    const double* f2 = e->d_f2part;
+    uint32_t nf2 = e->fp_grid;
+    if (multi) {
+        f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_f2part, e->fp_grid, e->d_f2, st_in);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+        SART_TRY(allreduce_f64(e, e->d_f2, 1, ncclSum));
+        f2 = e->d_f2;
+        nf2 = 1;
+    }
+    SART_TRY(launch_decide(e, t, f2, nf2, st_in, st_out));
+    if (last) return SART_OK;
+
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+    SART_TRY(launch_bp(e, st_out));
+    if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+    SART_TRY(launch_reduce(e, st_out));
+    SART_TRY(allreduce_f64(e, e->d_sred, e->V, ncclSum));
+    return launch_update(e, t, st_out);
 }
 
 // column reduction of the staged weights d_w into d_sred (reduced over ranks): initial guess / log-solver "obs"
@@ -410,26 +582,40 @@ int run_solve(sart_engine* e, int has_guess) {
     e->stats.iterate_ms = ms;
     e->stats.fp_ms_avg = e->stats.bp_ms_avg = 0;
     e->stats.fp_launches = e->stats.bp_launches = 0;
+    e->stats.fused_ms_avg = 0;
+    e->stats.fused_launches = 0;
+    e->stats.sweep_mode = e->fused ? SART_SWEEP_FUSED : SART_SWEEP_SPLIT;
     if (e->profiling) {
-        // every profiled sweep up to the deciding one has completed (they precede ev_batch[done_slot]); the deciding
-        // sweep ran its forward projection only
-        const int nfp = std::min(kProfiledSweeps, fin.iterations + 1);
-        const int nbp = std::min(kProfiledSweeps, fin.iterations);
-        double fp = 0, bp = 0;
-        for (int k = 0; k < nfp; ++k) {
+        // every profiled sweep up to the deciding one has completed (they precede ev_batch[done_slot]).
+        // Events [0],[1] bracket a forward projection, [2],[3] a back projection or a fused sweep.
+        const int nsweeps = std::min(kProfiledSweeps, fin.iterations + 1);  // sweeps 0 .. iterations
+        double fp = 0, second = 0;
+        int nfp = 0, nsecond = 0;
+        for (int k = 0; k < nsweeps; ++k) {
+            const bool last = k >= e->cfg.max_iterations;
+            const bool fused_sweep = e->fused && !last;
             float a = 0.f;
-            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][0], e->ev_prof[k][1]));
-            fp += a;
-        }
-        for (int k = 0; k < nbp; ++k) {
-            float b = 0.f;
-            CUDA_TRY(cudaEventElapsedTime(&b, e->ev_prof[k][2], e->ev_prof[k][3]));
-            bp += b;
+            if (!fused_sweep) {
+                CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][0], e->ev_prof[k][1]));
+                fp += a;
+                ++nfp;
+            }
+            // the deciding sweep of the split path ran its forward projection only; a fused sweep always ran whole
+            if (fused_sweep || (!last && k < fin.iterations)) {
+                CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][2], e->ev_prof[k][3]));
+                second += a;
+                ++nsecond;
+            }
         }
         e->stats.fp_ms_avg = nfp ? fp / nfp : 0;
-        e->stats.bp_ms_avg = nbp ? bp / nbp : 0;
         e->stats.fp_launches = nfp;
-        e->stats.bp_launches = nbp;
+        if (e->fused) {
+            e->stats.fused_ms_avg = nsecond ? second / nsecond : 0;
+            e->stats.fused_launches = nsecond;
+        } else {
+            e->stats.bp_ms_avg = nsecond ? second / nsecond : 0;
+            e->stats.bp_launches = nsecond;
+        }
     }
     return SART_OK;
 }
@@ -559,6 +745,7 @@ int create_impl(const sart_config* cfg, sart_engine* e) {
     e->cfg.device = e->device;
 
     SART_TRY(plan_launches(e));
+    SART_TRY(plan_fused(e));
 
     size_t free_b = 0, total_b = 0;
     CUDA_TRY(cudaMemGetInfo(&free_b, &total_b));
@@ -584,7 +771,7 @@ int create_impl(const sart_config* cfg, sart_engine* e) {
     SART_TRY(dev_alloc(&e->d_rinv, e->P));
     SART_TRY(dev_alloc(&e->d_fit, e->P));
     SART_TRY(dev_alloc(&e->d_w, e->P));
-    SART_TRY(dev_alloc(&e->d_part, (uint64_t)e->bp_slabs * e->ld));
+    SART_TRY(dev_alloc(&e->d_part, (uint64_t)std::max(e->bp_slabs, e->fu_nclusters) * e->ld));
     SART_TRY(dev_alloc(&e->d_fs, 1));
     CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_st), 2 * sizeof(IterState)));
 
@@ -662,6 +849,7 @@ int sart_create(const sart_config* cfg, sart_engine** out) {
     if (cfg->npixel == 0 || cfg->nvoxel == 0) return fail(SART_ERR_INVALID_ARGUMENT, "npixel and nvoxel must be positive");
     if (cfg->nranks < 1 || cfg->rank < 0 || cfg->rank >= cfg->nranks) return fail(SART_ERR_INVALID_ARGUMENT, "need 0 <= rank < nranks");
     if (cfg->semantics != SART_SEMANTICS_CPU && cfg->semantics != SART_SEMANTICS_GPU) return fail(SART_ERR_INVALID_ARGUMENT, "unknown semantics");
+    if (cfg->sweep_mode < SART_SWEEP_AUTO || cfg->sweep_mode > SART_SWEEP_FUSED) return fail(SART_ERR_INVALID_ARGUMENT, "unknown sweep_mode");
     SART_TRY(check_params(*cfg));
     sart_engine* e = new sart_engine();
     const int rc = create_impl(cfg, e);

@@ -1,0 +1,288 @@
+// Fused sweep: forward projection AND back projection from ONE pass over the matrix in HBM.
+//
+// The two sweeps of an iteration read the same matrix; what separates them is only that the back projection of row
+// i needs w_i, which needs the complete dot product of row i. A row of 50 000 - 200 000 voxels (200 - 800 KB) does not
+// fit one SM, but it fits a thread-block CLUSTER: the C CTAs of a cluster split the columns into C panels, each CTA
+// streams its panel of the cluster's current row into shared memory with one bulk-async copy (TMA, mbarrier
+// completion), multiplies it with its slice of x (held in registers), the C x NW per-warp partial dot products are
+// exchanged through distributed shared memory, every warp forms the same fit_i / w_i in the same order, and the row
+// panel -- still in shared memory -- is accumulated into the CTA's slice of s = H^T w (held in registers).
+// HBM is read once per iteration instead of twice; shared memory is read twice instead.
+//
+//   warp NW (producer, one lane): for each row: wait empty[stage] -> expect_tx(full[stage]) -> cp.async.bulk
+//   warps 0..NW-1 (consumers), software-pipelined so that the exchange latency of row t hides behind row t+1:
+//       FP(0); for t: { FP(t+1); FIN(t) }
+//       FP(t):  wait full[stage] ; partial dot from smem x registers ; warp sum ; lane q < C sends the partial into
+//               CTA q's slot [t mod 2S][my rank][warp] with st.async, which completes 4 bytes on CTA q's dot barrier
+//               (armed by CTA q's producer with expect_tx = 4*C*NW when it issues the row's copy)
+//       FIN(t): wait dot barrier ; fixed-order fp64 sum of the C*NW partials ; w_i ;
+//               s += row * w_i from smem ; arrive empty[stage]
+// No __syncthreads in the loop: warps only meet at the mbarriers. 2S dot slots make the slot of row t+2S reusable
+// only after every CTA has consumed row t. At the end each CTA writes its slice of the cluster's
+// partial s; the clusters' partials are added in fixed order by reduce_partials_kernel, exactly like the slabs of
+// the two-kernel path. Replaces cublasSgemv + cublasSdot + PropagateKernel's prologue and main loop
+// (source/sartsolver_cuda.cpp:239-253, source/cuda/sart_kernels.cu:63-101) in one launch.
+#pragma once
+
+#include "kernels.cuh"
+
+namespace sart {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_id_x() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%clusterid.x;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cluster_count_x() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%nclusterid.x;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local_addr, uint32_t cta) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta));
+    return r;
+}
+// Asynchronous store into another CTA's shared memory that completes 4 bytes of transaction on that CTA's mbarrier:
+// the waiter on the barrier sees the value, and no release fence is needed on the sending side. (A plain remote store
+// followed by mbarrier.arrive.release.cluster costs a MEMBAR.ALL.GPU per row per warp, which waits for every
+// outstanding global load of the warp -- measured 2 us per row.)
+__device__ __forceinline__ void st_async_remote_f32(uint32_t cluster_addr, float v, uint32_t cluster_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f32 [%0], %1, [%2];" ::"r"(cluster_addr),
+                 "f"(v), "r"(cluster_bar)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ float warp_sum_f32(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+    return v;
+}
+
+struct FusedArgs {
+    const float* H;        // [P][ld]
+    uint64_t ld4;          // ld / 4
+    uint64_t P;
+    const float* x;        // [ld]
+    const float* g;        // [P] normalised measurement
+    const float* rinv;     // [P]
+    float* part;           // [nclusters][ld] per-cluster partial back projection
+    double* f2part;        // [nclusters] per-cluster sum(fit^2)
+    const IterState* st;   // may be null
+    uint32_t Wc;           // float4 columns per CTA panel (last panel may be narrower)
+    uint32_t stages;       // S >= 2
+    uint32_t stage_bytes;  // bytes of one stage, multiple of 128
+    int log_mode;
+};
+
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float lds32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+
+// shared memory: [S stages of the row panel][2S x C x NW dot slots (float)][full[S], empty[S], dot[2S] mbarriers]
+// All ring / slot / barrier positions advance incrementally (no integer division in the row loop).
+template <int NT, int K>
+__global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs a) {
+    if (a.st && a.st->done) return;
+    constexpr uint32_t NW = NT / 32;
+    extern __shared__ __align__(128) unsigned char smem[];
+    const uint32_t S = a.stages;
+    const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
+    const uint32_t cid = cluster_id_x(), ncl = cluster_count_x();
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    const uint32_t nslot = C * NW;
+    const uint32_t ring_u32 = smem_u32(smem);
+    const uint32_t slots_u32 = ring_u32 + S * a.stage_bytes;
+    const uint32_t full_u32 = slots_u32 + 2 * S * nslot * 4, empty_u32 = full_u32 + 8 * S, dot_u32 = empty_u32 + 8 * S;
+
+    if (tid == 0) {
+        for (uint32_t s = 0; s < S; ++s) {
+            mbar_init(full_u32 + 8 * s, 1);
+            mbar_init(empty_u32 + 8 * s, NW);
+        }
+        for (uint32_t s = 0; s < 2 * S; ++s) mbar_init(dot_u32 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    cluster_sync_all();  // barriers of every CTA exist before anybody completes transactions on them remotely
+
+    const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;  // rows cid, cid + ncl, ...
+    const uint32_t c0 = rank * a.Wc;
+    const uint32_t wcols = (uint32_t)min((uint64_t)a.Wc, a.ld4 - c0);
+
+    if (warp == NW) {
+        // ---- producer ------------------------------------------------------------------------------------------------
+        if (lane == 0) {
+            const uint32_t bytes = wcols * 16;
+            const char* src = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
+            const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
+            uint32_t stage = 0, slot = 0, empty_parity = 1;  // parity 1 passes at once on the first lap
+            for (uint32_t t = 0; t < n; ++t) {
+                mbar_wait(empty_u32 + 8 * stage, empty_parity);
+                // the stage being free means every CTA has consumed row t - 2S: its dot slot can be armed for row t.
+                // Partials that peers send before this line just run the transaction count negative for a moment.
+                mbar_expect_tx(dot_u32 + 8 * slot, 4 * nslot);
+                mbar_expect_tx(full_u32 + 8 * stage, bytes);
+                bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
+                src += src_step;
+                if (++stage == S) {
+                    stage = 0;
+                    empty_parity ^= 1;
+                }
+                if (++slot == 2 * S) slot = 0;
+            }
+        }
+        __syncwarp();  // the whole warp reaches the closing cluster barrier together
+    } else {
+        // ---- consumers -----------------------------------------------------------------------------------------------
+        // this thread owns float4 columns tid, tid + NT, ... of the panel: `mine` of them (<= K)
+        const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
+        float4 xr[K], sacc[K];
+        {
+            const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x) + c0 + tid;
+#pragma unroll
+            for (int m = 0; m < K; ++m) {
+                xr[m] = (m < mine) ? __ldg(x4 + m * NT) : make_float4(0.f, 0.f, 0.f, 0.f);
+                sacc[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+        double f2acc = 0.0;
+
+        // where lane q < C delivers this warp's partial in CTA q: slot block base + (rank * NW + warp) * 4
+        const uint32_t peer = (lane < C) ? lane : 0;
+        const uint32_t peer_slot0 = map_to_cta(slots_u32 + (rank * NW + warp) * 4, peer);
+        const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
+
+        // ring positions of the forward (fp_*) and the finishing (fin_*) half of the pipeline
+        uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0;
+        uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
+        const float* gp = a.g + cid;
+        const float* rp = a.rinv + cid;
+        float g_cur = 0.f, r_cur = 0.f, g_nxt = 0.f, r_nxt = 0.f;
+
+        auto forward = [&](float& g_out, float& r_out) {
+            g_out = __ldg(gp);  // consumed one pipeline step later
+            r_out = __ldg(rp);
+            gp += ncl;
+            rp += ncl;
+            mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
+            const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int m = 0; m < K; ++m)
+                if (m < mine) {
+                    const float4 h = lds128(base + m * (NT * 16));
+                    a0 = fmaf(h.x, xr[m].x, a0);
+                    a1 = fmaf(h.y, xr[m].y, a1);
+                    a2 = fmaf(h.z, xr[m].z, a2);
+                    a3 = fmaf(h.w, xr[m].w, a3);
+                }
+            const float acc = warp_sum_f32((a0 + a1) + (a2 + a3));
+            if (lane < C) st_async_remote_f32(peer_slot0 + fp_slot * (nslot * 4), acc, peer_dot0 + 8 * fp_slot);
+            if (++fp_stage == S) {
+                fp_stage = 0;
+                fp_parity ^= 1;
+            }
+            if (++fp_slot == 2 * S) fp_slot = 0;
+        };
+
+        auto finish = [&](float gi, float ri) {
+            mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
+            // fixed-order sum of the C * NW partials: the same in every warp of every CTA -> identical fit everywhere
+            const uint32_t sl = slots_u32 + fin_slot * (nslot * 4) + lane * 4;
+            float p = 0.f;
+            for (uint32_t k = lane; k < nslot; k += 32) p += lds32(sl + (k - lane) * 4);
+            const float fitv = warp_sum_f32(p);
+            float wi = 0.f;
+            if (gi >= 0.f) wi = a.log_mode ? fitv * ri : (gi - fitv) * ri;
+            f2acc += (double)fitv * (double)fitv;
+            const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
+#pragma unroll
+            for (int m = 0; m < K; ++m)
+                if (m < mine) {
+                    const float4 h = lds128(base + m * (NT * 16));
+                    sacc[m].x = fmaf(h.x, wi, sacc[m].x);
+                    sacc[m].y = fmaf(h.y, wi, sacc[m].y);
+                    sacc[m].z = fmaf(h.z, wi, sacc[m].z);
+                    sacc[m].w = fmaf(h.w, wi, sacc[m].w);
+                }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty_u32 + 8 * fin_stage);
+            if (++fin_stage == S) fin_stage = 0;
+            if (++fin_slot == 2 * S) {
+                fin_slot = 0;
+                fin_parity ^= 1;
+            }
+        };
+
+        if (n > 0) {
+            forward(g_cur, r_cur);
+            for (uint32_t t = 0; t + 1 < n; ++t) {
+                forward(g_nxt, r_nxt);
+                finish(g_cur, r_cur);
+                g_cur = g_nxt;
+                r_cur = r_nxt;
+            }
+            finish(g_cur, r_cur);
+        }
+
+        float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part) + (uint64_t)cid * a.ld4 + c0 + tid;
+#pragma unroll
+        for (int m = 0; m < K; ++m)
+            if (m < mine) out4[m * NT] = sacc[m];
+        if (rank == 0 && tid == 0) a.f2part[cid] = f2acc;
+    }
+    cluster_sync_all();  // nobody leaves while a peer may still address its shared memory
+}
+
+}  // namespace sart

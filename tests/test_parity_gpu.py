@@ -12,6 +12,8 @@ from tests.cases import CASES, build_case, load_synthetic, rel_l2
 pytestmark = pytest.mark.gpu
 
 TOL = 1e-5
+SPLIT, FUSED = 1, 2  # SART_SWEEP_SPLIT / SART_SWEEP_FUSED
+BOTH_MODES = pytest.mark.parametrize("mode", [SPLIT, FUSED], ids=["split", "fused"])
 
 
 def _engine_for(sart, case, H=None, **extra):
@@ -39,11 +41,12 @@ def _run_frames(eng, case):
     return np.stack(xs), np.array(sts), np.array(its)
 
 
+@BOTH_MODES
 @pytest.mark.parametrize("name", list(CASES))
-def test_engine_matches_golden(name, sart, restatement, golden):
+def test_engine_matches_golden(name, mode, sart, restatement, golden):
     case = build_case(name, restatement)
     fixed = case["kw"]["conv_tolerance"] < 1e-20
-    with _engine_for(sart, case) as eng:
+    with _engine_for(sart, case, sweep_mode=mode) as eng:
         x, st, it = _run_frames(eng, case)
     gx, gst, git = golden[name + "/x"], golden[name + "/status"], golden[name + "/iterations"]
     if fixed:
@@ -104,14 +107,16 @@ def test_ray_sums_and_forward_projection_fp64(sart, restatement):
     assert rel_l2(fwd, restatement.forward(H, x)) < 1e-13
 
 
-@pytest.mark.parametrize("P,V,iters", [(4096, 2048, 20), (2050, 4100, 12), (33, 7, 15), (1, 40, 5)])
-def test_fixed_iterations_parity_across_shapes(P, V, iters, sart, restatement):
+@BOTH_MODES
+@pytest.mark.parametrize("P,V,iters", [(4096, 2048, 20), (2050, 4100, 12), (33, 7, 15), (1, 40, 5), (700, 20000, 8)])
+def test_fixed_iterations_parity_across_shapes(P, V, iters, mode, sart, restatement):
     syn = load_synthetic()
     H = restatement.fill_synthetic(P, V, 99)
     g = restatement.forward(H, syn.emission_profile(V))
     lap = syn.laplacian_coo(V)
     x_ref, st_ref, it_ref = restatement.solve(H, g, lap=lap, max_iterations=iters, fixed_iterations=True)
-    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=iters, fixed_iterations=True) as eng:
+    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=iters, fixed_iterations=True,
+                     sweep_mode=mode) as eng:
         eng.upload_rows(H)
         eng.set_laplacian(*lap)
         eng.finalize()
@@ -119,7 +124,9 @@ def test_fixed_iterations_parity_across_shapes(P, V, iters, sart, restatement):
         s = eng.stats()
     assert (st, it) == (st_ref, it_ref) == (sart.MAX_ITERATIONS_EXCEEDED, iters)
     assert rel_l2(x, x_ref) <= TOL
-    assert s.sweeps == 2 * iters + 2 and s.gpu_launches >= 5 * iters
+    assert s.sweep_mode == mode and s.sweeps == 2 * iters + 2 and s.gpu_launches >= 4 * iters
+    if mode == FUSED:
+        assert s.fused_launches == min(iters, 64) and s.bp_launches == 0 and s.fp_launches == 1
 
 
 def test_gpu_semantics_masked_initial_guess(sart, restatement):
@@ -171,14 +178,15 @@ def test_resident_path_and_setters(sart, restatement):
             eng.solve(g, np.zeros(V + 1))
 
 
-def test_convergence_decision_on_device_matches_oracle(sart, restatement):
+@BOTH_MODES
+def test_convergence_decision_on_device_matches_oracle(mode, sart, restatement):
     syn = load_synthetic()
     P, V = 1024, 512
     H = restatement.fill_synthetic(P, V, 8)
     g = restatement.forward(H, syn.emission_profile(V))
     x_ref, st_ref, it_ref, hist = restatement.solve(H, g, max_iterations=500, conv_tolerance=1e-4, history=True)
     assert st_ref == 0 and 3 < it_ref < 500
-    with sart.Engine(P, V, device=0, max_iterations=500, conv_tolerance=1e-4) as eng:
+    with sart.Engine(P, V, device=0, max_iterations=500, conv_tolerance=1e-4, sweep_mode=mode) as eng:
         eng.upload_rows(H)
         eng.finalize()
         x, st, it = eng.solve(g)
@@ -189,25 +197,30 @@ def test_convergence_decision_on_device_matches_oracle(sart, restatement):
         assert rel_l2(x, restatement.solve(H, g, max_iterations=it, fixed_iterations=True)[0]) <= TOL
 
 
-def test_same_voxel_count_as_the_bench_workload_on_a_row_subsample(sart, restatement):
+@pytest.mark.parametrize("mode,P,V", [(SPLIT, 512, 50000), (FUSED, 512, 50000), (FUSED, 300, 100000), (FUSED, 150, 150000)],
+                         ids=["split-50k", "fused-50k-cluster4", "fused-100k-cluster8", "fused-150k-cluster16"])
+def test_same_voxel_count_as_the_bench_workload_on_a_row_subsample(mode, P, V, sart, restatement):
     """BASELINE config 2 has 50 000 voxels; the oracle cannot hold its 200 000 rows, but the generator is keyed by
     global (row, column), so the first rows of that very matrix are a valid reduced problem with the same row
     length, panel count and padding."""
     syn = load_synthetic()
-    P, V, iters = 512, 50000, 6
+    iters = 6
     H = restatement.fill_synthetic(P, V, 42)
     g = restatement.forward(H, syn.emission_profile(V))
     lap = syn.laplacian_coo(V)
     x_ref = restatement.solve(H, g, lap=lap, max_iterations=iters, fixed_iterations=True)[0]
-    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=iters, fixed_iterations=True) as eng:
+    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=iters, fixed_iterations=True,
+                     sweep_mode=mode) as eng:
         eng.fill_synthetic(42)
         eng.set_laplacian(*lap)
         eng.finalize()
         x = eng.solve(g)[0]
+        assert eng.stats().sweep_mode == mode
     assert rel_l2(x, x_ref) <= TOL
 
 
-def test_full_size_properties_config2(sart):
+@BOTH_MODES
+def test_full_size_properties_config2(mode, sart):
     """BASELINE config 2 at full size (200 000 x 50 000 fp32 = 40 GB + Laplacian): properties that need no oracle.
     (1) bit-reproducible; (2) scale covariance solve(c g) = c solve(g); (3) a consistent frame g = H x* started at
     x* stays there (residual weights vanish), without the Laplacian."""
@@ -217,7 +230,8 @@ def test_full_size_properties_config2(sart):
         pytest.skip("needs ~46 GB of free device memory")
     syn = load_synthetic()
     xs = syn.emission_profile(V)
-    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=6, fixed_iterations=True) as eng:
+    with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=6, fixed_iterations=True,
+                     sweep_mode=mode) as eng:
         eng.fill_synthetic(42)
         eng.set_laplacian(*syn.laplacian_coo(V))
         eng.finalize()
@@ -259,3 +273,24 @@ def test_sweep_kernels_known_answers(P, V, sart):
     H64 = H.astype(np.float64)
     assert rel_l2(fit, H64 @ x.astype(np.float32).astype(np.float64)) < 2e-6
     assert rel_l2(s, H64.T @ w.astype(np.float32).astype(np.float64)) < 2e-6
+
+
+def test_fused_and_split_sweeps_agree_at_full_size(sart):
+    """The two ways of passing over the matrix are the same arithmetic in a different summation order: on the full
+    BASELINE config-2 matrix their solutions must agree far inside the parity tolerance."""
+    info = sart.device_query(0)
+    P, V = 200000, 50000
+    if info.free_mem < P * V * 4 + (6 << 30):
+        pytest.skip("needs ~46 GB of free device memory")
+    syn = load_synthetic()
+    xs = syn.emission_profile(V)
+    sols = []
+    for mode in (SPLIT, FUSED):
+        with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=10, fixed_iterations=True,
+                         sweep_mode=mode) as eng:
+            eng.fill_synthetic(42)
+            eng.set_laplacian(*syn.laplacian_coo(V))
+            eng.finalize()
+            g = eng.forward_project(xs)
+            sols.append(eng.solve(g)[0])
+    assert rel_l2(sols[1], sols[0]) <= 1e-6
