@@ -30,10 +30,15 @@ def main():
         return eng
 
     first = True
-    for name, P, V, kw, use_lap, saturated in [
-        ("linear_fixed", 1030, 515, dict(max_iterations=20, fixed_iterations=True), True, False),
-        ("linear_tol", 777, 300, dict(max_iterations=400, conv_tolerance=1e-4), False, True),
-        ("log_fixed", 900, 256, dict(max_iterations=15, fixed_iterations=True, logarithmic=True, relaxation=0.7), True, False),
+    SPLIT, FUSED = 1, 2
+    for name, P, V, kw, use_lap, saturated, mode in [
+        ("linear_fixed", 1030, 515, dict(max_iterations=20, fixed_iterations=True), True, False, SPLIT),
+        ("linear_fixed_fused", 1030, 515, dict(max_iterations=20, fixed_iterations=True), True, False, FUSED),
+        ("linear_tol", 777, 300, dict(max_iterations=400, conv_tolerance=1e-4), False, True, SPLIT),
+        ("linear_tol_fused", 777, 300, dict(max_iterations=400, conv_tolerance=1e-4), False, True, FUSED),
+        ("wide_fused_cluster2", 300, 20000, dict(max_iterations=6, fixed_iterations=True), True, False, FUSED),
+        ("log_fixed", 900, 256, dict(max_iterations=15, fixed_iterations=True, logarithmic=True, relaxation=0.7), True, False, SPLIT),
+        ("log_fixed_fused", 900, 256, dict(max_iterations=15, fixed_iterations=True, logarithmic=True, relaxation=0.7), True, False, FUSED),
     ]:
         H = res.fill_synthetic(P, V, 31)
         g = res.forward(H, syn.emission_profile(V))
@@ -42,7 +47,7 @@ def main():
         lap = syn.laplacian_coo(V) if use_lap else None
         okw = dict(kw)
         x_ref, st_ref, it_ref = res.solve(H, g, lap=lap, beta_laplace=2e-2, nranks=cp.world, **okw)
-        eng = make_engine(P, V, beta_laplace=2e-2, **kw)
+        eng = make_engine(P, V, beta_laplace=2e-2, sweep_mode=mode, **kw)
         # NCCL allows one communicator per engine; every engine of this worker needs its own id
         if not first:
             uid = cp.broadcast_bytes(sart.comm_unique_id() if cp.rank == 0 else None)
