@@ -113,7 +113,7 @@ class ClockSampler:
 
 # ---- the reference's CPU path on a bounded sample -------------------------------------------------------------------
 
-def cpu_baseline(npixel, nvoxel, iterations=4, sample_rows=4096, threads=None):
+def cpu_baseline(npixel, nvoxel, iterations=4, sample_rows=4096, threads=None, laplacian=True):
     """Times the reference's own CPU solver (oracle/_ref, or the C restatement when that is not built) on the first
     ``sample_rows`` rows of the very same matrix, all voxels, Laplacian on, warm start, ``iterations`` iterations, one
     thread-rank per host core, and extrapolates linearly in the row count (the per-iteration cost is a sweep of the
@@ -126,7 +126,7 @@ def cpu_baseline(npixel, nvoxel, iterations=4, sample_rows=4096, threads=None):
     H = res.fill_synthetic(rows, nvoxel, SEED)
     xs = syn.emission_profile(nvoxel)
     g = res.forward(H, xs)
-    lap = syn.laplacian_coo(nvoxel)
+    lap = syn.laplacian_coo(nvoxel) if laplacian else None
     x0 = 0.9 * xs + 0.01
     if Reference.available():
         kind = "reference"
@@ -147,7 +147,7 @@ def cpu_baseline(npixel, nvoxel, iterations=4, sample_rows=4096, threads=None):
     value = sample_rate * rows / npixel
     return {
         "value": value, "unit": UNIT, "cores": ranks if kind == "reference" else cores, "kind": kind,
-        "sample": (f"rows 0..{rows - 1} of the same {npixel}x{nvoxel} matrix (all voxels, Laplacian on, warm start), "
+        "sample": (f"rows 0..{rows - 1} of the same {npixel}x{nvoxel} matrix (all voxels, Laplacian {'on' if laplacian else 'off'}, warm start), "
                    f"{done} iterations in {t_solve:.2f} s on {ranks} thread-rank(s) = {sample_rate:.3f} it/s on the sample, "
                    f"scaled by {rows}/{npixel} rows; constructor sums {t_ctor:.2f} s not counted"),
         "sample_seconds": t_solve,
@@ -158,7 +158,8 @@ def run_reference_arm(args):
     vals, last = [], None
     t0 = time.perf_counter()
     for i in range(args.warmup + args.steps):
-        last = cpu_baseline(args.npixel, args.nvoxel, iterations=args.cpu_iterations, sample_rows=args.cpu_rows)
+        last = cpu_baseline(args.npixel, args.nvoxel, iterations=args.cpu_iterations, sample_rows=args.cpu_rows,
+                            threads=args.cpu_ranks or None, laplacian=args.laplacian)
         if i >= args.warmup:
             vals.append(last)
         if time.perf_counter() - t0 > 240 and vals:
@@ -179,12 +180,15 @@ def run_reference_arm(args):
 
 
 def workload_config(args, n):
+    gb = args.npixel * args.nvoxel * 4 / 1e9
     return {
-        "workload": f"BASELINE configs[1]: synthetic {args.npixel}x{args.nvoxel} fp32 ray-transfer matrix "
-                    f"({args.npixel * args.nvoxel * 4 / 1e9:.1f} GB) + Laplacian, row-sharded over the GPUs",
+        "workload": f"BASELINE {args.workload_name}: synthetic {args.npixel}x{args.nvoxel} fp32 ray-transfer matrix "
+                    f"({gb:.1f} GB){' + Laplacian' if args.laplacian else ''}, row-sharded over the GPUs",
         "npixel": args.npixel, "nvoxel": args.nvoxel, "iterations_per_step": args.iterations, "warm_start": True,
-        "laplacian": True, "beta_laplace": BETA, "seed": SEED, "sharding": f"rows/{max(n, 1)} (source/main.cpp:67-68)",
-        "l2_policy": "matrix >> L2 (126 MB); no flush needed between sweeps",
+        "laplacian": args.laplacian, "beta_laplace": BETA, "seed": SEED,
+        "sharding": f"rows/{max(n, 1)} (source/main.cpp:67-68)",
+        "l2_policy": ("matrix >> L2 (126 MB); no flush needed between sweeps" if gb > 1.0 else
+                      "matrix ~ L2-sized: sweeps partly hit in L2, so the HBM roofline can be exceeded; not flushed"),
     }
 
 
@@ -203,7 +207,7 @@ def run_engine_arm(args, cp):
         uid = cp.broadcast_bytes(sart.comm_unique_id() if cp.rank == 0 else None)
         eng.comm_init(uid)
     eng.fill_synthetic(SEED)
-    if cp.rank == 0 or cp.world == 1:
+    if args.laplacian and cp.rank == 0:
         eng.set_laplacian(*syn.laplacian_coo(V))  # the reference reads it on rank 0 only; finalize shares it
     eng.finalize()
 
@@ -296,7 +300,8 @@ def run_engine_arm(args, cp):
 
     cb = None
     if cp.rank == 0 and cp.world == 1 and not args.no_cpu_baseline:
-        cb = cpu_baseline(P, V, iterations=args.cpu_iterations, sample_rows=args.cpu_rows)
+        cb = cpu_baseline(P, V, iterations=args.cpu_iterations, sample_rows=args.cpu_rows, threads=args.cpu_ranks or None,
+                          laplacian=args.laplacian)
         cb.pop("sample_seconds", None)
 
     if cp.rank == 0:
@@ -329,7 +334,16 @@ def main():
     ap.add_argument("--cpu-iterations", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--sweep", default="auto", choices=["auto", "split", "fused"])
+    ap.add_argument("--cpu-ranks", type=int, default=0, help="thread-ranks of the CPU baseline (0 = all host cores)")
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1"],
+                    help="c2: BASELINE configs[1] (the headline, default); c1: configs[0], 8192x4096, 100 iterations, "
+                         "no Laplacian, CPU reference on the whole problem with 2 ranks")
     args = ap.parse_args()
+    args.laplacian, args.workload_name = True, "configs[1]"
+    if args.workload == "c1":
+        args.npixel, args.nvoxel, args.iterations = 8192, 4096, 100
+        args.cpu_rows, args.cpu_iterations, args.cpu_ranks = 8192, 100, args.cpu_ranks or 2
+        args.laplacian, args.workload_name = False, "configs[0]"
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":

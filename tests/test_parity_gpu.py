@@ -294,3 +294,20 @@ def test_fused_and_split_sweeps_agree_at_full_size(sart):
             g = eng.forward_project(xs)
             sols.append(eng.solve(g)[0])
     assert rel_l2(sols[1], sols[0]) <= 1e-6
+
+
+@BOTH_MODES
+def test_baseline_config1_full(mode, sart, restatement):
+    """BASELINE configs[0] at full size: 8192 x 4096, single frame, 100 iterations, default initial guess, against the
+    oracle after exactly 100 iterations."""
+    syn = load_synthetic()
+    P, V, iters = 8192, 4096, 100
+    H = restatement.fill_synthetic(P, V, 42)
+    g = restatement.forward(H, syn.emission_profile(V))
+    x_ref, st_ref, it_ref = restatement.solve(H, g, max_iterations=iters, fixed_iterations=True)
+    with sart.Engine(P, V, device=0, max_iterations=iters, fixed_iterations=True, sweep_mode=mode) as eng:
+        eng.fill_synthetic(42)
+        eng.finalize()
+        x, st, it = eng.solve(g)
+    assert (st, it) == (st_ref, it_ref)
+    assert rel_l2(x, x_ref) <= TOL
