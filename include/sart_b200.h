@@ -42,7 +42,7 @@ extern "C" {
 /* How one iteration passes over the matrix (no reference counterpart; results agree within the parity tolerance).
  * SPLIT: forward projection and back projection as two kernels, two reads of the shard from HBM.
  * FUSED: one cluster kernel that keeps each row in shared memory between its forward and back projection, one read
- *        of the shard from HBM; needs nvoxel <= 245 760 (16 CTAs x 3840 float4 columns). AUTO picks FUSED for long rows. */
+ *        of the shard from HBM; needs nvoxel <= 229 376 (16 CTAs x 3584 float4 columns). AUTO picks FUSED for long rows. */
 #define SART_SWEEP_AUTO 0
 #define SART_SWEEP_SPLIT 1
 #define SART_SWEEP_FUSED 2

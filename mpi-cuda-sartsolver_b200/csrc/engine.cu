@@ -204,20 +204,15 @@ int plan_launches(sart_engine* e) {
 
 typedef void (*FusedKernel)(const FusedArgs);
 
-// Consumer-thread counts the fused kernel is built for. One extra warp produces, and registers are handed out per
-// SM sub-partition (16 K each), so 15 + 1 warps leave 128 registers per thread and 7 + 1 warps leave 255.
-// K = float4 columns a consumer thread owns (its slice of x and of s lives in registers): the smallest K that covers
-// the panel is used.
-template <int NT, int KMAX>
-struct FusedFamily {
-    template <int K>
-    static FusedKernel pick(int k) {
-        if constexpr (K > KMAX) return nullptr;
-        else return (k <= K) ? fused_sweep_kernel<NT, K> : pick<K + 1>(k);
-    }
-};
-constexpr int kFusedThreadsWide = 480, kFusedKWide = 8;      // 16 warps, <= 128 registers
-constexpr int kFusedThreadsNarrow = 224, kFusedKNarrow = 16;  // 8 warps, <= 255 registers
+// 14 consumer warps + producer + reducer = 16 warps (see fused.cuh). K = float4 columns a consumer thread owns (its
+// slices of x and s live in registers): the smallest K that covers the panel is instantiated.
+constexpr int kFusedKMax = 8;
+constexpr int kFusedThreads = 448;  // consumer threads
+template <int K>
+FusedKernel pick_fused_kernel(int k) {
+    if constexpr (K > kFusedKMax) return nullptr;
+    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K> : pick_fused_kernel<K + 1>(k);
+}
 
 // Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
 // registers (<= K float4 per thread), as many shared-memory stages of one row panel as fit, and as many clusters as
@@ -226,9 +221,8 @@ int plan_fused(sart_engine* e) {
     e->fused = false;
     const int mode = e->cfg.sweep_mode;
     if (mode == SART_SWEEP_SPLIT) return SART_OK;
-    const bool narrow = env_int("SART_FUSED_THREADS", kFusedThreadsWide) == kFusedThreadsNarrow;
-    const uint32_t nt = narrow ? kFusedThreadsNarrow : kFusedThreadsWide;
-    const uint64_t max_wc = (uint64_t)nt * (narrow ? kFusedKNarrow : kFusedKWide);
+    const uint32_t nt = kFusedThreads;
+    const uint64_t max_wc = (uint64_t)nt * kFusedKMax;
     uint32_t C = 0;
     for (uint32_t c : {1u, 2u, 4u, 8u, 16u})
         if (ceil_div(e->ld4, c) <= max_wc) {
@@ -245,12 +239,14 @@ int plan_fused(sart_engine* e) {
     const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
     const uint32_t stage_bytes = (uint32_t)(ceil_div((uint64_t)wc * 16, 128) * 128);
     const uint32_t nw = nt / 32;
+    const uint32_t extra_warps = 2;  // producer + reducer
     int max_smem = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
     uint32_t S = 0, smem = 0;
     const uint32_t s_cap = (uint32_t)std::max(2, env_int("SART_FUSED_STAGES", 8));
     for (uint32_t s = s_cap; s >= 2; --s) {
-        const uint64_t need = (uint64_t)s * stage_bytes + (uint64_t)2 * s * C * nw * 4 + (uint64_t)4 * s * 8;
+        // stages + warp partials [2S][NWC] + per-CTA sums [2S][16] + barriers full[S], empty[S], wbar[2S], dot[2S]
+        const uint64_t need = (uint64_t)s * stage_bytes + (uint64_t)2 * s * nw * 4 + (uint64_t)2 * s * 16 * 4 + (uint64_t)6 * s * 8;
         if (need <= (uint64_t)max_smem) {
             S = s;
             smem = (uint32_t)need;
@@ -262,11 +258,10 @@ int plan_fused(sart_engine* e) {
     if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 2048)) return SART_OK;
 
     const int k_need = (int)ceil_div(wc, nt);
-    const FusedKernel kFusedKernel = narrow ? FusedFamily<kFusedThreadsNarrow, kFusedKNarrow>::pick<1>(k_need)
-                                            : FusedFamily<kFusedThreadsWide, kFusedKWide>::pick<1>(k_need);
+    const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need);
     if (!kFusedKernel) return unavailable("no kernel instance for this panel width");
     e->fu_kernel = kFusedKernel;
-    e->fu_threads = nt;
+    e->fu_threads = nt + 32 * extra_warps;
     CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (C > 8) CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg = {};
@@ -276,7 +271,7 @@ int plan_fused(sart_engine* e) {
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.gridDim = dim3(C * (uint32_t)e->sm_count, 1, 1);
-    cfg.blockDim = dim3(nt + 32, 1, 1);
+    cfg.blockDim = dim3(nt + 32 * extra_warps, 1, 1);
     cfg.dynamicSmemBytes = smem;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
@@ -321,7 +316,7 @@ int launch_fused(sart_engine* e, const float* x, const IterState* st) {
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.gridDim = dim3(e->fu_cluster * e->fu_nclusters, 1, 1);
-    cfg.blockDim = dim3(e->fu_threads + 32, 1, 1);
+    cfg.blockDim = dim3(e->fu_threads, 1, 1);
     cfg.dynamicSmemBytes = e->fu_smem;
     cfg.stream = e->stream;
     cfg.attrs = attr;

@@ -4,24 +4,32 @@
 // i needs w_i, which needs the complete dot product of row i. A row of 50 000 - 200 000 voxels (200 - 800 KB) does not
 // fit one SM, but it fits a thread-block CLUSTER: the C CTAs of a cluster split the columns into C panels, each CTA
 // streams its panel of the cluster's current row into shared memory with one bulk-async copy (TMA, mbarrier
-// completion), multiplies it with its slice of x (held in registers), the C x NW per-warp partial dot products are
-// exchanged through distributed shared memory, every warp forms the same fit_i / w_i in the same order, and the row
+// completion), multiplies it with its slice of x (held in registers), the per-CTA partial dot products are
+// exchanged through distributed shared memory, every thread forms the same fit_i / w_i in the same order, and the row
 // panel -- still in shared memory -- is accumulated into the CTA's slice of s = H^T w (held in registers).
 // HBM is read once per iteration instead of twice; shared memory is read twice instead.
 //
-//   warp NW (producer, one lane): for each row: wait empty[stage] -> expect_tx(full[stage]) -> cp.async.bulk
-//   warps 0..NW-1 (consumers), software-pipelined so that the exchange latency of row t hides behind row t+1:
+//   producer warp (one lane): per row: wait empty[stage] -> arm the row's dot barrier (expect_tx 4*C) -> expect_tx
+//       (full[stage]) -> cp.async.bulk of the panel (50 KB at 50 000 voxels, 4 CTAs)
+//   consumer warps, software-pipelined so that the exchange latency of row t hides behind row t+1:
 //       FP(0); for t: { FP(t+1); FIN(t) }
-//       FP(t):  wait full[stage] ; partial dot from smem x registers ; warp sum ; lane q < C sends the partial into
-//               CTA q's slot [t mod 2S][my rank][warp] with st.async, which completes 4 bytes on CTA q's dot barrier
-//               (armed by CTA q's producer with expect_tx = 4*C*NW when it issues the row's copy)
-//       FIN(t): wait dot barrier ; fixed-order fp64 sum of the C*NW partials ; w_i ;
-//               s += row * w_i from smem ; arrive empty[stage]
-// No __syncthreads in the loop: warps only meet at the mbarriers. 2S dot slots make the slot of row t+2S reusable
-// only after every CTA has consumed row t. At the end each CTA writes its slice of the cluster's
-// partial s; the clusters' partials are added in fixed order by reduce_partials_kernel, exactly like the slabs of
-// the two-kernel path. Replaces cublasSgemv + cublasSdot + PropagateKernel's prologue and main loop
-// (source/sartsolver_cuda.cpp:239-253, source/cuda/sart_kernels.cu:63-101) in one launch.
+//       FP(t):  wait full[stage] ; partial dot from smem x registers ; warp sum ; lane 0 stores it into the CTA's
+//               warp-partial slot and arrives on the CTA-local barrier wbar[slot]
+//       FIN(t): wait dot[slot] ; add the C per-CTA sums in rank order (one or a few broadcast 128-bit loads: the same
+//               additions in every thread of the cluster, so fit_i is identical everywhere) ; w_i ;
+//               s += row * w_i from the same smem stage ; arrive empty[stage]
+//   reducer warp: per row: wait wbar[slot] ; fixed-order sum of the CTA's warp partials ; lanes q < C send it into
+//       CTA q's slot [t mod 2S][rank] with st.async ... mbarrier::complete_tx (DSMEM). One message per CTA pair and row:
+//       an earlier version let every warp send to every CTA (C x NW messages per row and CTA), which cost 2 % at C = 4
+//       and 20 % at C = 16. No fence anywhere: a plain remote store + mbarrier.arrive.release.cluster is a
+//       MEMBAR.ALL.GPU per row per warp and made the first version 2x slower than two separate sweeps.
+// No __syncthreads in the loop: warps only meet at mbarriers. Slot reuse: a CTA reaches FP(t) only after its own
+// FIN(t-S), which needed every peer's row t-S, which those peers produced after their FIN(t-S-2); with 2S slots (S >= 2)
+// nothing for row t can land before every CTA has consumed row t-2S, and the producer re-arms a slot when it re-issues
+// the stage. At the end each CTA writes its slice of the cluster's partial s; the clusters' partials are added in
+// fixed order by reduce_partials_kernel, exactly like the slabs of the two-kernel path. Replaces cublasSgemv +
+// cublasSdot + PropagateKernel's prologue and main loop (source/sartsolver_cuda.cpp:239-253,
+// source/cuda/sart_kernels.cu:63-101) in one launch.
 #pragma once
 
 #include "kernels.cuh"
@@ -129,49 +137,54 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
     return v;
 }
 
-// shared memory: [S stages of the row panel][2S x C x NW dot slots (float)][full[S], empty[S], dot[2S] mbarriers]
+// warps 0..NWC-1 consumers, warp NWC TMA producer, warp NWC+1 reducer: 16 warps in all, so that every SM sub-partition
+// holds 4 and a thread may use 128 registers (a 17th warp caps the kernel at 96 and spills).
+// shared memory: [S stages][2S x NWC warp partials][2S x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
 // All ring / slot / barrier positions advance incrementally (no integer division in the row loop).
 template <int NT, int K>
-__global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs a) {
+__global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
     if (a.st && a.st->done) return;
-    constexpr uint32_t NW = NT / 32;
+    constexpr uint32_t NWC = NT / 32;
+    constexpr uint32_t CSTRIDE = 16;  // floats per slot of per-CTA sums (cluster size <= 16), 64-byte aligned
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t S = a.stages;
     const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
     const uint32_t cid = cluster_id_x(), ncl = cluster_count_x();
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    const uint32_t nslot = C * NW;
     const uint32_t ring_u32 = smem_u32(smem);
-    const uint32_t slots_u32 = ring_u32 + S * a.stage_bytes;
-    const uint32_t full_u32 = slots_u32 + 2 * S * nslot * 4, empty_u32 = full_u32 + 8 * S, dot_u32 = empty_u32 + 8 * S;
+    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][NWC] floats
+    const uint32_t cdot_u32 = wpart_u32 + 2 * S * NWC * 4;           // [2S][CSTRIDE] floats
+    const uint32_t full_u32 = cdot_u32 + 2 * S * CSTRIDE * 4;
+    const uint32_t empty_u32 = full_u32 + 8 * S, wbar_u32 = empty_u32 + 8 * S, dot_u32 = wbar_u32 + 16 * S;
 
     if (tid == 0) {
         for (uint32_t s = 0; s < S; ++s) {
             mbar_init(full_u32 + 8 * s, 1);
-            mbar_init(empty_u32 + 8 * s, NW);
+            mbar_init(empty_u32 + 8 * s, NWC);
         }
-        for (uint32_t s = 0; s < 2 * S; ++s) mbar_init(dot_u32 + 8 * s, 1);
+        for (uint32_t s = 0; s < 2 * S; ++s) {
+            mbar_init(wbar_u32 + 8 * s, NWC);
+            mbar_init(dot_u32 + 8 * s, 1);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    cluster_sync_all();  // barriers of every CTA exist before anybody completes transactions on them remotely
+    cluster_sync_all();
 
-    const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;  // rows cid, cid + ncl, ...
+    const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;
     const uint32_t c0 = rank * a.Wc;
     const uint32_t wcols = (uint32_t)min((uint64_t)a.Wc, a.ld4 - c0);
 
-    if (warp == NW) {
+    if (warp == NWC) {
         // ---- producer ------------------------------------------------------------------------------------------------
         if (lane == 0) {
             const uint32_t bytes = wcols * 16;
             const char* src = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
             const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
-            uint32_t stage = 0, slot = 0, empty_parity = 1;  // parity 1 passes at once on the first lap
+            uint32_t stage = 0, slot = 0, empty_parity = 1;
             for (uint32_t t = 0; t < n; ++t) {
                 mbar_wait(empty_u32 + 8 * stage, empty_parity);
-                // the stage being free means every CTA has consumed row t - 2S: its dot slot can be armed for row t.
-                // Partials that peers send before this line just run the transaction count negative for a moment.
-                mbar_expect_tx(dot_u32 + 8 * slot, 4 * nslot);
+                mbar_expect_tx(dot_u32 + 8 * slot, 4 * C);  // one float from every CTA of the cluster
                 mbar_expect_tx(full_u32 + 8 * stage, bytes);
                 bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
                 src += src_step;
@@ -182,10 +195,26 @@ __global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs
                 if (++slot == 2 * S) slot = 0;
             }
         }
-        __syncwarp();  // the whole warp reaches the closing cluster barrier together
+        __syncwarp();
+    } else if (warp == NWC + 1) {
+        // ---- reducer: CTA-level sum of the warp partials, one message per peer -----------------------------------------
+        const uint32_t peer = (lane < C) ? lane : 0;
+        const uint32_t peer_cdot0 = map_to_cta(cdot_u32 + rank * 4, peer);
+        const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
+        uint32_t slot = 0, parity = 0;
+        for (uint32_t t = 0; t < n; ++t) {
+            mbar_wait(wbar_u32 + 8 * slot, parity);
+            float p = (lane < NWC) ? lds32(wpart_u32 + (slot * NWC + lane) * 4) : 0.f;
+            p = warp_sum_f32(p);  // fixed tree over the NWC partials
+            if (lane < C) st_async_remote_f32(peer_cdot0 + slot * (CSTRIDE * 4), p, peer_dot0 + 8 * slot);
+            if (++slot == 2 * S) {
+                slot = 0;
+                parity ^= 1;
+            }
+        }
+        __syncwarp();
     } else {
         // ---- consumers -----------------------------------------------------------------------------------------------
-        // this thread owns float4 columns tid, tid + NT, ... of the panel: `mine` of them (<= K)
         const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
         float4 xr[K], sacc[K];
         {
@@ -197,21 +226,15 @@ __global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs
             }
         }
         double f2acc = 0.0;
-
-        // where lane q < C delivers this warp's partial in CTA q: slot block base + (rank * NW + warp) * 4
-        const uint32_t peer = (lane < C) ? lane : 0;
-        const uint32_t peer_slot0 = map_to_cta(slots_u32 + (rank * NW + warp) * 4, peer);
-        const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
-
-        // ring positions of the forward (fp_*) and the finishing (fin_*) half of the pipeline
         uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0;
         uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
         const float* gp = a.g + cid;
         const float* rp = a.rinv + cid;
         float g_cur = 0.f, r_cur = 0.f, g_nxt = 0.f, r_nxt = 0.f;
+        const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
 
         auto forward = [&](float& g_out, float& r_out) {
-            g_out = __ldg(gp);  // consumed one pipeline step later
+            g_out = __ldg(gp);
             r_out = __ldg(rp);
             gp += ncl;
             rp += ncl;
@@ -228,7 +251,10 @@ __global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs
                     a3 = fmaf(h.w, xr[m].w, a3);
                 }
             const float acc = warp_sum_f32((a0 + a1) + (a2 + a3));
-            if (lane < C) st_async_remote_f32(peer_slot0 + fp_slot * (nslot * 4), acc, peer_dot0 + 8 * fp_slot);
+            if (lane == 0) {
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + (fp_slot * NWC + warp) * 4), "f"(acc) : "memory");
+                mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partial
+            }
             if (++fp_stage == S) {
                 fp_stage = 0;
                 fp_parity ^= 1;
@@ -238,11 +264,16 @@ __global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs
 
         auto finish = [&](float gi, float ri) {
             mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
-            // fixed-order sum of the C * NW partials: the same in every warp of every CTA -> identical fit everywhere
-            const uint32_t sl = slots_u32 + fin_slot * (nslot * 4) + lane * 4;
-            float p = 0.f;
-            for (uint32_t k = lane; k < nslot; k += 32) p += lds32(sl + (k - lane) * 4);
-            const float fitv = warp_sum_f32(p);
+            // the C per-CTA sums in rank order: the same additions in every thread of the cluster
+            float fitv = 0.f;
+            const uint32_t cd = cdot_u32 + fin_slot * (CSTRIDE * 4);
+            for (uint32_t q = 0; q < c4; ++q) {
+                const float4 v = lds128(cd + q * 16);
+                fitv += v.x;
+                if (4 * q + 1 < C) fitv += v.y;
+                if (4 * q + 2 < C) fitv += v.z;
+                if (4 * q + 3 < C) fitv += v.w;
+            }
             float wi = 0.f;
             if (gi >= 0.f) wi = a.log_mode ? fitv * ri : (gi - fitv) * ri;
             f2acc += (double)fitv * (double)fitv;
@@ -282,7 +313,7 @@ __global__ void __launch_bounds__(NT + 32, 1) fused_sweep_kernel(const FusedArgs
             if (m < mine) out4[m * NT] = sacc[m];
         if (rank == 0 && tid == 0) a.f2part[cid] = f2acc;
     }
-    cluster_sync_all();  // nobody leaves while a peer may still address its shared memory
+    cluster_sync_all();
 }
 
 }  // namespace sart
