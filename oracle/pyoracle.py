@@ -15,6 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(_HERE, "libsart_oracle.so")
 REF_SO = os.path.join(_HERE, "_ref", "libsart_ref.so")
+REF_GPU_SO = os.path.join(_HERE, "_ref", "libsart_ref_gpu.so")  # the reference's own CUDA solver, built for sm_100a
 
 SUCCESS = 0
 MAX_ITERATIONS_EXCEEDED = -1

@@ -27,6 +27,11 @@
 #include <vector>
 
 #include "sartsolver.hpp"
+#ifdef REF_WITH_CUDA
+// second build of this harness (oracle/_ref/libsart_ref_gpu.so): the reference's own GPU solver, i.e. its
+// source/sartsolver_cuda.cpp + source/cuda/sart_kernels.cu compiled for sm_100a in place, as the kernel to beat
+#include "sartsolver_cuda.hpp"
+#endif
 
 namespace {
 
@@ -164,8 +169,13 @@ int ref_sart_solve_frames(const float* H, uint64_t npixel, uint64_t nvoxel, cons
         team.barrier();
         auto t0 = std::chrono::steady_clock::now();
         BaseSARTSolverMPI* solver;
+#ifdef REF_WITH_CUDA
+        if (logarithmic) solver = new LogSARTSolverMPICuda(raytransfer, laplacian, rank);
+        else solver = new SARTSolverMPICuda(raytransfer, laplacian, rank);
+#else
         if (logarithmic) solver = new LogSARTSolverMPI(raytransfer, laplacian);
         else solver = new SARTSolverMPI(raytransfer, laplacian);
+#endif
         solver->set_ray_density_threshold(params[0]);
         solver->set_ray_length_threshold(params[1]);
         solver->set_convolution_tolerance(params[2]);
@@ -191,7 +201,12 @@ int ref_sart_solve_frames(const float* H, uint64_t npixel, uint64_t nvoxel, cons
             if (rank == 0) {
                 std::copy(solution_vec.begin(), solution_vec.end(), x + (size_t)f * nvoxel);
                 status[f] = st;
+#ifdef REF_WITH_CUDA
+                // GPU path: two scalar reductions before the loop (max, sum g^2: sartsolver_cuda.cpp:149, 156), one per pass
+                iterations[f] = (int)(t_ctx.scalar_allreduce_calls - 2);
+#else
                 iterations[f] = (int)(t_ctx.scalar_allreduce_calls - 1);
+#endif
             }
             if (no_guess) solution_vec.clear();  // source/main.cpp:139
         }
