@@ -120,7 +120,8 @@ class Reference:
     def solve_frames(self, H, frames, x0=None, lap=None, no_guess=False, ray_density_threshold=1e-6,
                      ray_length_threshold=1e-6, conv_tolerance=1e-5, beta_laplace=2e-2, relaxation=1.0,
                      max_iterations=2000, logarithmic=False, nranks=1):
-        """frames [F][P] -> (x [F][V], status [F], iterations [F], (ctor_seconds, solve_seconds))."""
+        """frames [F][P] -> (x [F][V], status [F], iterations [F], (ctor_seconds, solve_seconds)); the wall time of
+        each frame's solve is left in ``self.frame_seconds``."""
         P, V = H.shape
         frames = np.ascontiguousarray(np.atleast_2d(frames), dtype=np.float64)
         F = frames.shape[0]
@@ -129,7 +130,7 @@ class Reference:
             x[0] = x0
         status = np.zeros(F, dtype=np.int32)
         iters = np.zeros(F, dtype=np.int32)
-        secs = np.zeros(2)
+        secs = np.zeros(2 + F)
         prm = np.array([ray_density_threshold, ray_length_threshold, conv_tolerance, beta_laplace, relaxation])
         li, lv, nnz, _keep = _lap_args(lap)
         rc = self.lib.ref_sart_solve_frames(H, P, V, li, lv, nnz, frames, x, F, 0 if x0 is None else 1,
@@ -137,6 +138,7 @@ class Reference:
                                             status.ctypes.data_as(C.c_void_p), iters.ctypes.data_as(C.c_void_p), secs)
         if rc != 0:
             raise ValueError("reference would reject these arguments (sartsolver.cpp:63-123)")
+        self.frame_seconds = secs[2:].copy()
         return x, status, iters, (secs[0], secs[1])
 
     def solve(self, H, g, x0=None, **kw):

@@ -130,7 +130,8 @@ extern "C" {
 // status, iterations [nframes] out. iterations = number of passes through the reference's iteration loop,
 //          recovered from the shim (each pass makes exactly one scalar MPI_Allreduce: sartsolver.cpp:222 / :329,
 //          plus one before the loop: :164 / :268).
-// seconds  [2] out: {constructor wall time, total solve wall time} as seen by rank 0.
+// seconds  [2 + nframes] out: {constructor wall time, total solve wall time, solve wall time of each frame} as seen
+//          by rank 0.
 // Returns 0, or -1 for arguments the reference would std::exit(1) on (sartsolver.cpp:63-123).
 int ref_sart_solve_frames(const float* H, uint64_t npixel, uint64_t nvoxel, const uint64_t* lap_idx,
                           const float* lap_val, uint64_t lap_nnz, const double* g, double* x, int nframes,
@@ -198,6 +199,7 @@ int ref_sart_solve_frames(const float* H, uint64_t npixel, uint64_t nvoxel, cons
             team.barrier();
             auto s1 = std::chrono::steady_clock::now();
             solve_seconds += std::chrono::duration<double>(s1 - s0).count();
+            if (rank == 0 && seconds) seconds[2 + f] = std::chrono::duration<double>(s1 - s0).count();
             if (rank == 0) {
                 std::copy(solution_vec.begin(), solution_vec.end(), x + (size_t)f * nvoxel);
                 status[f] = st;

@@ -311,3 +311,30 @@ def test_baseline_config1_full(mode, sart, restatement):
         x, st, it = eng.solve(g)
     assert (st, it) == (st_ref, it_ref)
     assert rel_l2(x, x_ref) <= TOL
+
+
+def test_engine_matches_the_reference_gpu_solver(sart, restatement):
+    """Second oracle: the reference's own CUDA solver (sartsolver_cuda.cpp + sart_kernels.cu + cuBLAS), compiled
+    unmodified for sm_100a into oracle/_ref/libsart_ref_gpu.so. Its stopping iteration under a vanishing tolerance is
+    run-dependent (fp32 sum(fit^2), atomics), so the engine is run for exactly the count the reference reached."""
+    import os
+    from oracle.pyoracle import REF_GPU_SO, Reference
+    if not os.path.exists(REF_GPU_SO):
+        pytest.skip("oracle/_ref/libsart_ref_gpu.so not built")
+    syn = load_synthetic()
+    P, V = 3000, 1500
+    H = restatement.fill_synthetic(P, V, 77)
+    g = restatement.forward(H, syn.emission_profile(V))
+    g[::11] = -1.0  # saturated pixels: the GPU path clips them out of the initial guess
+    lap = syn.laplacian_coo(V)
+    ref = Reference(REF_GPU_SO)
+    x_ref, st_ref, it_ref = ref.solve(H, g, lap=lap, beta_laplace=2e-2, max_iterations=8, conv_tolerance=1e-300)
+    assert 1 <= it_ref <= 8
+    for mode in (SPLIT, FUSED):
+        with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=it_ref, fixed_iterations=True,
+                         semantics=sart.SEMANTICS_GPU, sweep_mode=mode) as eng:
+            eng.upload_rows(H)
+            eng.set_laplacian(*lap)
+            eng.finalize()
+            x = eng.solve(g)[0]
+        assert rel_l2(x, x_ref) <= TOL
