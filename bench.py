@@ -243,6 +243,7 @@ def run_engine_arm(args, cp):
         bp_n += s.bp_launches
         fu_n += s.fused_launches
     sweep_mode = {1: "split", 2: "fused"}.get(s.sweep_mode, "?")
+    exchange_mode = {0: "none", 1: "nccl", 2: "peer-memory kernel"}.get(s.exchange_mode, "?")
     cp.barrier()
     w1 = time.perf_counter()
     clocks = sampler.summary(w0, w1) if sampler else None
@@ -310,7 +311,7 @@ def run_engine_arm(args, cp):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": cp.world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(args, cp.world), sweep=sweep_mode), "e2e": e2e, "gpu_launches": launches,
+            "config": dict(workload_config(args, cp.world), sweep=sweep_mode, exchange=exchange_mode), "e2e": e2e, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cb, "clocks": clocks,
             "wall_ms_per_step": wall_ms / args.steps, "per_rank": gathered,
             "device": {"name": info.name.decode(), "sms": info.sm_count, "l2_bytes": info.l2_bytes,

@@ -47,6 +47,15 @@ extern "C" {
 #define SART_SWEEP_SPLIT 1
 #define SART_SWEEP_FUSED 2
 
+/* How the per-iteration sum over the row shards travels between the GPUs of one box (replaces the reference's
+ * D2H -> MPI_Allreduce -> H2D, source/sartsolver_cuda.cpp:242-244): PEER = one kernel per rank that adds all ranks'
+ * partial vectors straight out of each other's memory over NVLink (CUDA IPC mappings made in sart_comm_init), takes the
+ * stop/continue decision and updates the solution; NCCL = ncclAllReduce + separate kernels (always used by the
+ * two-kernel sweep, and whenever the peers cannot be mapped or SART_EXCHANGE=nccl is set in the environment). */
+#define SART_EXCHANGE_NONE 0
+#define SART_EXCHANGE_NCCL 1
+#define SART_EXCHANGE_PEER 2
+
 #define SART_UNIQUE_ID_BYTES 128
 
 typedef struct sart_engine sart_engine;
@@ -89,6 +98,8 @@ typedef struct sart_stats {
     double fused_ms_avg;     /* mean duration of one fused forward+back projection launch (SART_SWEEP_FUSED) */
     int32_t fused_launches;  /* launches behind fused_ms_avg */
     int32_t sweep_mode;      /* SART_SWEEP_SPLIT or SART_SWEEP_FUSED: what the engine runs */
+    int32_t exchange_mode;   /* SART_EXCHANGE_*: how the per-iteration reduction over the ranks travels */
+    int32_t reserved;
 } sart_stats;
 
 typedef struct sart_device_info {

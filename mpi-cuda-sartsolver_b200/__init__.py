@@ -19,6 +19,7 @@ SUCCESS = 0
 MAX_ITERATIONS_EXCEEDED = -1
 SEMANTICS_CPU, SEMANTICS_GPU = 0, 1
 SWEEP_AUTO, SWEEP_SPLIT, SWEEP_FUSED = 0, 1, 2
+EXCHANGE_NONE, EXCHANGE_NCCL, EXCHANGE_PEER = 0, 1, 2
 UNIQUE_ID_BYTES = 128
 
 # every symbol include/sart_b200.h declares (tests check the library exports exactly these)
@@ -51,6 +52,7 @@ class Stats(C.Structure):
         ("fp_launches", C.c_int32), ("bp_launches", C.c_int32),
         ("matrix_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
         ("fused_ms_avg", C.c_double), ("fused_launches", C.c_int32), ("sweep_mode", C.c_int32),
+        ("exchange_mode", C.c_int32), ("reserved", C.c_int32),
     ]
 
 

@@ -119,6 +119,13 @@ struct sart_engine {
     bool profiling = true;
 
     ncclComm_t comm = nullptr;
+    // peer-memory exchange (one region per rank, mapped by every rank through CUDA IPC); see xchg_decide_update_kernel
+    char* d_xchg = nullptr;             // this rank's region
+    char** d_peers = nullptr;           // device array [nranks]: every rank's region as mapped here
+    std::vector<void*> peer_mappings;   // what cudaIpcOpenMemHandle returned (to close)
+    uint64_t xchg_buf_off[2] = {0, 0};
+    unsigned long long xchg_epoch = 0;
+    bool peer_exchange = false;
     bool measurement_staged = false, guess_staged = false;
     int launches = 0;
     sart_stats stats{};
@@ -196,7 +203,9 @@ int plan_launches(sart_engine* e) {
     e->bp_slabs = (uint32_t)ceil_div(e->P, e->bp_rows_per_slab);
 
     // sweeps per status poll: enough work per poll that the host round trip hides behind the next batch
-    const double sweep_us = 2.0 * (double)e->P * (double)e->ld * 4.0 / 6.0e6;  // at ~6 TB/s
+    // (from the global shape, so that every rank enqueues -- and therefore joins collectives -- in identical batches)
+    const double rows_per_rank = std::ceil((double)e->cfg.npixel / (double)e->cfg.nranks);
+    const double sweep_us = 2.0 * rows_per_rank * (double)e->ld * 4.0 / 6.0e6;  // at ~6 TB/s
     e->batch = std::min(16, std::max(1, (int)std::ceil(400.0 / std::max(sweep_us, 1.0))));
     e->batch = std::max(1, env_int("SART_BATCH", e->batch));
     return SART_OK;
@@ -362,9 +371,11 @@ int launch_bp(sart_engine* e, const IterState* st) {
     return SART_OK;
 }
 
-int launch_reduce(sart_engine* e, const IterState* st, uint32_t nslabs = 0) {
+int launch_reduce(sart_engine* e, const IterState* st, uint32_t nslabs = 0, double* dst = nullptr,
+                  const double* f2part = nullptr, uint32_t nf2 = 0) {
     const uint32_t blocks = (uint32_t)ceil_div(e->V, 256);
-    reduce_partials_kernel<<<blocks, 256, 0, e->stream>>>(e->d_part, nslabs ? nslabs : e->bp_slabs, e->ld, e->V, e->d_sred, st);
+    reduce_partials_kernel<<<blocks, 256, 0, e->stream>>>(e->d_part, nslabs ? nslabs : e->bp_slabs, e->ld, e->V,
+                                                          dst ? dst : e->d_sred, st, f2part, nf2);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
@@ -381,7 +392,7 @@ int allreduce_f64(sart_engine* e, double* buf, uint64_t count, ncclRedOp_t op) {
 // One sweep for the iterate x_t: forward projection, decision, and -- unless t is the last possible sweep, where
 // the decision can only be "stop" -- back projection, reduction and update. Kernels after the decision test the
 // freshly written state, so nothing but the forward projection runs once the solve is over.
-int launch_update(sart_engine* e, int t, const IterState* st) {
+UpdArgs make_update_args(sart_engine* e, int t, const IterState* st) {
     UpdArgs u;
     u.sred = e->d_sred;
     u.xd_cur = e->d_xd[t & 1];
@@ -401,7 +412,31 @@ int launch_update(sart_engine* e, int t, const IterState* st) {
     u.eps_norm = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 1.e-7 : 0.0;
     u.eps_orig = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 0.0 : 1.e-100;
     u.log_mode = e->cfg.logarithmic;
-    update_kernel<<<(uint32_t)ceil_div(e->V, 256), 256, 0, e->stream>>>(u);
+    return u;
+}
+
+int launch_update(sart_engine* e, int t, const IterState* st) {
+    update_kernel<<<(uint32_t)ceil_div(e->V, 256), 256, 0, e->stream>>>(make_update_args(e, t, st));
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+    return SART_OK;
+}
+
+// reduction over ranks + decision + update in one kernel over peer memory (fused sweep, several ranks, IPC available)
+int launch_xchg_update(sart_engine* e, int t, const IterState* st_in, IterState* st_out) {
+    XchgArgs x;
+    x.peers = e->d_peers;
+    x.nranks = (uint32_t)e->cfg.nranks;
+    x.rank = (uint32_t)e->cfg.rank;
+    x.epoch = e->xchg_epoch;
+    x.buf_off = e->xchg_buf_off[e->xchg_epoch & 1];
+    x.st_in = st_in;
+    x.st_out = st_out;
+    x.tol = e->cfg.conv_tolerance;
+    x.max_iter = e->cfg.max_iterations;
+    x.fixed = e->cfg.fixed_iterations;
+    x.t = t;
+    xchg_decide_update_kernel<<<(uint32_t)ceil_div(e->V, 256), 256, 0, e->stream>>>(x, make_update_args(e, t, nullptr));
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
@@ -442,6 +477,12 @@ int enqueue_sweep(sart_engine* e, int t) {
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
         SART_TRY(launch_fused(e, e->d_xf[t & 1], st_in));
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        if (multi && e->peer_exchange) {
+            ++e->xchg_epoch;  // same count on every rank: batches are enqueued identically (plan_launches)
+            double* buf = reinterpret_cast<double*>(e->d_xchg + e->xchg_buf_off[e->xchg_epoch & 1]);
+            SART_TRY(launch_reduce(e, st_in, e->fu_nclusters, buf, e->d_f2part, e->fu_nclusters));
+            return launch_xchg_update(e, t, st_in, st_out);
+        }
         SART_TRY(launch_reduce(e, st_in, e->fu_nclusters));
         const double* f2 = e->d_f2part;
         uint32_t nf2 = e->fu_nclusters;
@@ -564,6 +605,8 @@ int run_solve(sart_engine* e, int has_guess) {
         }
     }
     const IterState fin = e->h_st[done_slot];
+    if (fin.status == kStatusExchangeTimeout)
+        return fail(SART_ERR_NCCL, "peer-memory exchange timed out: a rank of the job did not reach the reduction");
 
     finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_xd[0], e->d_xd[1], e->d_st[t & 1], e->d_fs, e->d_xio, e->V);
     CUDA_TRY(cudaGetLastError());
@@ -580,6 +623,8 @@ int run_solve(sart_engine* e, int has_guess) {
     e->stats.fused_ms_avg = 0;
     e->stats.fused_launches = 0;
     e->stats.sweep_mode = e->fused ? SART_SWEEP_FUSED : SART_SWEEP_SPLIT;
+    e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE
+                             : (e->fused && e->peer_exchange) ? SART_EXCHANGE_PEER : SART_EXCHANGE_NCCL;
     if (e->profiling) {
         // every profiled sweep up to the deciding one has completed (they precede ev_batch[done_slot]).
         // Events [0],[1] bracket a forward projection, [2],[3] a back projection or a fused sweep.
@@ -693,6 +738,78 @@ int require(sart_engine* e, bool finalized) {
     return SART_OK;
 }
 
+// Maps every rank's exchange region into this process (CUDA IPC over NVLink). All ranks of one box only; when the
+// mapping is not possible (SART_EXCHANGE=nccl, more than 16 ranks, IPC refused) the engine keeps the NCCL all-reduce.
+// COLLECTIVE: every rank takes the same decision, because the outcome is all-reduced (MIN) before it is adopted.
+int setup_peer_exchange(sart_engine* e) {
+    NcclApi* api = nccl_api();
+    const char* mode = std::getenv("SART_EXCHANGE");
+    int ok = !(mode && std::string(mode) == "nccl") && e->cfg.nranks <= kMaxPeers;
+    const uint64_t flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
+    const uint64_t buf_bytes = ceil_div((e->V + 2) * sizeof(double), 256) * 256;
+    e->xchg_buf_off[0] = flags_bytes;
+    e->xchg_buf_off[1] = flags_bytes + buf_bytes;
+
+    cudaIpcMemHandle_t mine;
+    std::memset(&mine, 0, sizeof(mine));
+    if (ok) {
+        if (cudaMalloc(reinterpret_cast<void**>(&e->d_xchg), flags_bytes + 2 * buf_bytes) != cudaSuccess ||
+            cudaMemsetAsync(e->d_xchg, 0, flags_bytes + 2 * buf_bytes, e->stream) != cudaSuccess ||
+            cudaIpcGetMemHandle(&mine, e->d_xchg) != cudaSuccess) {
+            (void)cudaGetLastError();
+            ok = 0;
+        }
+    }
+    // handles of all ranks (the zeroed flags are ordered before the handle leaves this rank: same stream)
+    const int n = e->cfg.nranks;
+    char *d_mine = nullptr, *d_all = nullptr;
+    SART_TRY(dev_alloc(&d_mine, sizeof(mine), false));
+    SART_TRY(dev_alloc(&d_all, sizeof(mine) * n, false));
+    CUDA_TRY(cudaMemcpyAsync(d_mine, &mine, sizeof(mine), cudaMemcpyHostToDevice, e->stream));
+    NCCL_TRY(api, api->AllGather(d_mine, d_all, sizeof(mine), ncclChar, e->comm, e->stream));
+    std::vector<cudaIpcMemHandle_t> all(n);
+    CUDA_TRY(cudaMemcpyAsync(all.data(), d_all, sizeof(mine) * n, cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    CUDA_TRY(cudaFree(d_mine));
+    CUDA_TRY(cudaFree(d_all));
+
+    std::vector<char*> peers(n, nullptr);
+    e->peer_mappings.assign(n, nullptr);
+    for (int r = 0; r < n && ok; ++r) {
+        if (r == e->cfg.rank) {
+            peers[r] = e->d_xchg;
+            continue;
+        }
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            (void)cudaGetLastError();
+            ok = 0;
+            break;
+        }
+        e->peer_mappings[r] = p;
+        peers[r] = static_cast<char*>(p);
+    }
+    // adopt the peer path only if every rank managed to map every region
+    double* d_ok = nullptr;
+    SART_TRY(dev_alloc(&d_ok, 1, false));
+    const double mine_ok = ok ? 1.0 : 0.0;
+    double all_ok = 0.0;
+    CUDA_TRY(cudaMemcpyAsync(d_ok, &mine_ok, sizeof(double), cudaMemcpyHostToDevice, e->stream));
+    NCCL_TRY(api, api->AllReduce(d_ok, d_ok, 1, ncclDouble, ncclMin, e->comm, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(&all_ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaStreamSynchronize(e->stream));
+    CUDA_TRY(cudaFree(d_ok));
+    if (all_ok < 0.5) {
+        e->peer_exchange = false;
+        return SART_OK;
+    }
+    SART_TRY(dev_alloc(&e->d_peers, (uint64_t)n, false));
+    CUDA_TRY(cudaMemcpy(e->d_peers, peers.data(), sizeof(char*) * n, cudaMemcpyHostToDevice));
+    e->xchg_epoch = 0;
+    e->peer_exchange = true;
+    return SART_OK;
+}
+
 void free_engine(sart_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
@@ -701,6 +818,10 @@ void free_engine(sart_engine* e) {
         NcclApi* api = nccl_api();
         if (api) api->CommDestroy(e->comm);
     }
+    for (void* p : e->peer_mappings)
+        if (p) cudaIpcCloseMemHandle(p);
+    if (e->d_xchg) cudaFree(e->d_xchg);
+    if (e->d_peers) cudaFree(e->d_peers);
     void* ptrs[] = {e->dH, e->d_rho, e->d_lambda, e->d_lap_rowptr, e->d_lap_col, e->d_lap_val, e->d_gd, e->d_xio,
                     e->d_obs, e->d_sred, e->d_f2part, e->d_f2, e->d_xd[0], e->d_xd[1], e->d_xf[0], e->d_xf[1], e->d_g,
                     e->d_rinv, e->d_fit, e->d_w, e->d_part, e->d_fs, e->d_st[0], e->d_st[1]};
@@ -882,7 +1003,7 @@ int sart_comm_init(sart_engine* e, const uint8_t id[SART_UNIQUE_ID_BYTES]) {
     ncclUniqueId uid;
     std::memcpy(&uid, id, sizeof(uid));
     NCCL_TRY(api, api->CommInitRank(&e->comm, e->cfg.nranks, uid, e->cfg.rank));
-    return SART_OK;
+    return setup_peer_exchange(e);
 }
 
 int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64_t col0, uint64_t ncols,

@@ -252,9 +252,18 @@ __global__ void __launch_bounds__(NT) bp_cols_kernel(const BpArgs a) {
 }
 
 // s_j = sum over slabs (fixed order, fp64) -> sred[j]
+// When f2part is given, warp 0 of block 0 also adds the nf2 partials of sum(fit^2) into sred[V] (one launch less
+// where the scalar travels with the vector).
 __global__ void reduce_partials_kernel(const float* __restrict__ part, uint32_t nslabs, uint64_t ld, uint64_t V,
-                                       double* __restrict__ sred, const IterState* st) {
+                                       double* __restrict__ sred, const IterState* st,
+                                       const double* __restrict__ f2part = nullptr, uint32_t nf2 = 0) {
     if (st && st->done) return;
+    if (f2part && blockIdx.x == 0 && threadIdx.x < 32) {
+        double f = 0.0;
+        for (uint32_t k = threadIdx.x; k < nf2; k += 32) f += f2part[k];
+        f = warp_sum(f);
+        if (threadIdx.x == 0) sred[V] = f;
+    }
     const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= V) return;
     double s = 0.0;
@@ -349,11 +358,8 @@ struct UpdArgs {
     int log_mode;
 };
 
-__global__ void update_kernel(const UpdArgs a) {
-    if (a.st->done) return;
-    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= a.V) return;
-
+// x_{t+1,j} from x_t and the reduced back projection s_j of voxel j
+__device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, double sj) {
     double pen = 0.0;
     if (a.lap_rowptr) {
         const int b = a.lap_rowptr[j], e = a.lap_rowptr[j + 1];
@@ -366,16 +372,137 @@ __global__ void update_kernel(const UpdArgs a) {
     const bool on = rho > a.h_d;
     double xn;
     if (!a.log_mode) {
-        const double diff = on ? a.sred[j] * (a.relax / rho) : 0.0;
+        const double diff = on ? sj * (a.relax / rho) : 0.0;
         xn = a.xd_cur[j] + (diff - pen);
         if (signbit(xn)) xn = 0.0;
     } else {
-        const double fitj = on ? a.sred[j] : 0.0;
+        const double fitj = on ? sj : 0.0;
         const double eps = a.eps_norm + a.eps_orig / a.fs->norm;
         xn = a.xd_cur[j] * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
     }
     a.xd_next[j] = xn;
     a.xf_next[j] = (float)xn;
+}
+
+__global__ void update_kernel(const UpdArgs a) {
+    if (a.st->done) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= a.V) return;
+    apply_update(a, j, a.sred[j]);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Cross-GPU reduction + decision + update in ONE kernel over NVLink peer memory (replaces the D2H -> MPI_Allreduce ->
+// H2D round trip of the reference, sartsolver_cuda.cpp:242-244 and :253-255, and this engine's own
+// reduce -> ncclAllReduce -> decide -> update launch chain when the ranks can map each other's memory).
+// Every rank owns an exchange region that all ranks of the box map through CUDA IPC:
+//     [nranks flags, 128 B apart][buffer 0: V + 1 doubles][buffer 1: V + 1 doubles]
+// Sweep number `epoch` uses buffer epoch & 1. Before this kernel the rank's own reduced back projection s[V] and its
+// sum(fit^2) have been written to its buffer (reduce_partials_kernel). Then
+//   1. block 0 publishes `epoch` into flag[rank] of EVERY rank's region (release, system scope);
+//   2. every block waits until all of its own region's flags have reached `epoch` (acquire, system scope): all
+//      partial vectors are then complete and visible;
+//   3. every thread adds the nranks values of its voxel in rank order (peer loads over NVLink, L1-bypassing), so all
+//      ranks obtain the bit-identical sum, takes the same stop/continue decision from the summed sum(fit^2), and
+//      applies the update for its voxel.
+// Buffer reuse needs no second barrier: a rank overwrites buffer b two sweeps later, after it has passed step 2 of
+// the sweep in between, which every peer only signals once it has finished reading buffer b.
+// A peer that never arrives (crashed rank) ends the wait after ~4 s with status SART_STATUS_EXCHANGE_TIMEOUT.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kMaxPeers = 16;
+constexpr int kFlagStride = 128;
+constexpr int kStatusExchangeTimeout = -3;
+
+struct XchgArgs {
+    char* const* peers;  // [nranks] base address of every rank's exchange region as mapped in THIS process
+    uint32_t nranks, rank;
+    unsigned long long epoch;
+    uint64_t buf_off;  // byte offset of this epoch's buffer inside a region
+    const IterState* st_in;
+    IterState* st_out;
+    double tol;
+    int max_iter, fixed, t;
+};
+
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs x, const UpdArgs u) {
+    const IterState s = *x.st_in;
+    const bool writer = (blockIdx.x == 0 && threadIdx.x == 0);
+    if (s.done) {
+        if (writer) *x.st_out = s;
+        return;
+    }
+    __shared__ int timed_out;
+    __shared__ double f2r[kMaxPeers];
+    if (threadIdx.x == 0) timed_out = 0;
+    __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x < x.nranks) {
+        __threadfence_system();
+        st_release_sys_u64(reinterpret_cast<unsigned long long*>(x.peers[threadIdx.x] + x.rank * kFlagStride), x.epoch);
+    }
+    if (threadIdx.x < x.nranks) {
+        const unsigned long long* flag =
+            reinterpret_cast<const unsigned long long*>(x.peers[x.rank] + threadIdx.x * kFlagStride);
+        const long long t0 = clock64();
+        while (ld_acquire_sys_u64(flag) < x.epoch) {
+            if (clock64() - t0 > 8000000000LL) {  // ~4 s at 2 GHz
+                timed_out = 1;
+                break;
+            }
+        }
+        // this rank's sum(fit^2), straight from the owner's buffer
+        f2r[threadIdx.x] = __ldcv(reinterpret_cast<const double*>(x.peers[threadIdx.x] + x.buf_off) + u.V);
+    }
+    __syncthreads();
+
+    IterState o = s;
+    bool stop = false;
+    if (timed_out) {
+        stop = true;
+        o.status = kStatusExchangeTimeout;
+    } else if (x.t >= 1) {
+        double f2 = 0.0;
+        for (uint32_t r = 0; r < x.nranks; ++r) f2 += f2r[r];
+        const double m2 = u.fs->m2;
+        const double conv = (m2 - f2) / m2;
+        const int iter = x.t - 1;
+        if (!x.fixed && iter >= 1 && fabs(conv - s.conv_prev) < x.tol) {
+            stop = true;
+            o.status = 0;
+        } else if (x.t >= x.max_iter) {
+            stop = true;
+            o.status = -1;
+        }
+        o.conv_prev = conv;
+    }
+    if (stop) {
+        o.done = 1;
+        o.iterations = x.t;
+        o.final_buf = x.t & 1;
+    } else {
+        o.k = x.t + 1;
+    }
+    if (writer) *x.st_out = o;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (stop || j >= u.V) return;
+
+    double part[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+        if (r < (int)x.nranks) part[r] = __ldcv(reinterpret_cast<const double*>(x.peers[r] + x.buf_off) + j);
+    double sj = 0.0;
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+        if (r < (int)x.nranks) sj += part[r];
+    apply_update(u, j, sj);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

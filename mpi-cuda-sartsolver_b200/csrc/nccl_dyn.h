@@ -1,6 +1,6 @@
 // NCCL entry points resolved with dlopen at first use, so that libsart_b200.so has no link-time NCCL dependency:
 // a single-GPU caller never needs the library, and a process that already carries an NCCL (e.g. one that imported
-// torch) shares that copy. Types come from <nccl.h>; only the six calls below are used.
+// torch) shares that copy. Types come from <nccl.h>; only the calls below are used.
 #pragma once
 
 #include <dlfcn.h>
@@ -18,6 +18,7 @@ struct NcclApi {
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
     std::string error;  // why loading failed, empty when usable
 };
@@ -52,6 +53,7 @@ inline NcclApi* nccl_api() {
         api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
         api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
         api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(sym("ncclBroadcast"));
+        api.AllGather = reinterpret_cast<decltype(api.AllGather)>(sym("ncclAllGather"));
         api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
     });
     return api.error.empty() ? &api : nullptr;

@@ -62,6 +62,7 @@ def main():
         rho, lam = eng.ray_sums()
         rho_ref, lam_ref = res.ray_sums(H, cp.world)
         x, st, it = eng.solve(g[off:off + n])
+        exchange = eng.stats().exchange_mode
         # warm-started second frame
         x2, st2, it2 = eng.solve(1.1 * g[off:off + n], x)
         x2_ref, st2_ref, it2_ref = res.solve(H, 1.1 * g, x0=x_ref, lap=lap, beta_laplace=2e-2, nranks=cp.world, **okw)
@@ -70,7 +71,7 @@ def main():
             "rho": rel_l2(rho, rho_ref), "lam": rel_l2(lam, lam_ref[off:off + n]),
             "x": rel_l2(x, x_ref), "status": [st, st_ref], "iterations": [it, it_ref],
             "x2": rel_l2(x2, x2_ref), "iterations2": [it2, it2_ref],
-            "x_hash": float(np.sum(x * np.arange(1, V + 1))),
+            "x_hash": float(np.sum(x * np.arange(1, V + 1))), "exchange": exchange, "mode": mode,
         }
     gathered = cp.gather(out)
     cp.barrier()

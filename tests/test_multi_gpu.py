@@ -44,4 +44,10 @@ def test_sharded_solve_matches_oracle(world):
             if c["iterations2"][0] == c["iterations2"][1]:
                 assert c["x2"] <= 1e-5, (name, c)
             hashes.add(c["x_hash"])
+            # the fused sweep reduces over peer memory (one kernel), the two-kernel sweep over NCCL
+            import os as _os
+            if c["mode"] == 2 and _os.environ.get("SART_EXCHANGE") != "nccl":
+                assert c["exchange"] == 2, (name, c)
+            else:
+                assert c["exchange"] == 1, (name, c)
         assert len(hashes) == 1, f"{name}: ranks ended with different solutions"

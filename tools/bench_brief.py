@@ -10,7 +10,7 @@ for line in sys.stdin:
         continue
     d = json.loads(line)
     k = d["roofline"]["kernels"]
-    parts = [f"N={d['n_gpus']} sweep={d['config'].get('sweep')} value={d['value']:.2f} it/s e2e={d['e2e']['value']:.2f} ms/step={d['ms_per_step']:.3f}"]
+    parts = [f"N={d['n_gpus']} sweep={d['config'].get('sweep')} exchange={d['config'].get('exchange')} value={d['value']:.2f} it/s e2e={d['e2e']['value']:.2f} ms/step={d['ms_per_step']:.3f}"]
     for name, v in k.items():
         if v["launches"]:
             parts.append(f"{name}: {v['ms']:.3f} ms x{v['launches']} alg {v['gbs']:.0f} GB/s hbm {v['hbm_gbs']:.0f} GB/s share {v['share_of_step']:.3f}")
