@@ -140,6 +140,14 @@ int sart_comm_init(sart_engine* e, const uint8_t id[SART_UNIQUE_ID_BYTES]);
  * Returns after the copy has completed. */
 int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64_t col0, uint64_t ncols,
                      const float* src, uint64_t src_ld);
+/* The same from a file, without a host-resident copy of the matrix: the block rows [local_row0, +nrows) x columns
+ * [col0, +ncols) is streamed from a raw little-endian fp32 array (row-major, file_ld floats per row, first element at
+ * byte file_offset of `path`) through a ring of three pinned staging buffers (SART_STAGING_MB each, default 64): the
+ * pread of slab k+1 overlaps the asynchronous copy of slab k, and host memory stays O(staging) however large the shard
+ * is (the reference holds the whole rank-local matrix in host RAM: source/include/raytransfer.hpp:20, and copies it in
+ * one blocking cudaMemcpy: source/sartsolver_cuda.cpp:104-106). Returns when the block is on the device. */
+int sart_load_rows_file(sart_engine* e, const char* path, uint64_t file_offset, uint64_t file_ld, uint64_t local_row0,
+                        uint64_t nrows, uint64_t col0, uint64_t ncols);
 /* Test/bench helpers without a reference counterpart: counter-based synthetic matrix keyed by GLOBAL row and
  * column (shard-invariant), and read-back of shard rows (dst leading dimension nvoxel). */
 int sart_fill_synthetic(sart_engine* e, uint64_t seed);

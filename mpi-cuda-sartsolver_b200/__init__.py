@@ -30,7 +30,7 @@ SYMBOLS = [
     "sart_set_ray_length_threshold", "sart_set_convolution_tolerance", "sart_set_beta_laplace", "sart_set_relaxation",
     "sart_set_max_iterations", "sart_set_fixed_iterations", "sart_get_config", "sart_solve", "sart_stage_measurement",
     "sart_stage_guess", "sart_solve_resident", "sart_fetch_solution", "sart_forward_project", "sart_get_stats",
-    "sart_kernel_forward", "sart_kernel_backward", "sart_back_project_noalloc",
+    "sart_kernel_forward", "sart_kernel_backward", "sart_back_project_noalloc", "sart_load_rows_file",
 ]
 
 
@@ -92,6 +92,7 @@ def lib():
         L.sart_comm_init.argtypes = [_vp, _vp]
         L.sart_upload_rows.argtypes = [_vp, _u64, _u64, _u64, _u64, _vp, _u64]
         L.sart_fill_synthetic.argtypes = [_vp, _u64]
+        L.sart_load_rows_file.argtypes = [_vp, C.c_char_p, _u64, _u64, _u64, _u64, _u64, _u64]
         L.sart_download_rows.argtypes = [_vp, _u64, _u64, _vp]
         L.sart_set_laplacian_coo.argtypes = [_vp, _vp, _vp, _u64]
         L.sart_finalize.argtypes = [_vp]
@@ -203,6 +204,9 @@ class Engine:
             block = np.ascontiguousarray(block)
         check(lib().sart_upload_rows(self._h, local_row0, block.shape[0], col0, block.shape[1],
                                      block.ctypes.data_as(C.c_void_p), block.strides[0] // 4))
+
+    def load_rows_file(self, path, file_offset, file_ld, local_row0, nrows, col0, ncols):
+        check(lib().sart_load_rows_file(self._h, os.fsencode(path), file_offset, file_ld, local_row0, nrows, col0, ncols))
 
     def fill_synthetic(self, seed):
         check(lib().sart_fill_synthetic(self._h, seed))

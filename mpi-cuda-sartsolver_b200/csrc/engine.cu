@@ -6,7 +6,11 @@
 // frame, sartsolver_cuda.cpp:160-191, 223, 267-271); a solve is a fixed sequence of launches on one stream with the
 // convergence decision taken on the device, polled by the host once per batch of sweeps.
 // There is no CPU fallback: without a CUDA device sart_create fails.
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <algorithm>
+#include <cerrno>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -126,6 +130,11 @@ struct sart_engine {
     uint64_t xchg_buf_off[2] = {0, 0};
     unsigned long long xchg_epoch = 0;
     bool peer_exchange = false;
+    // pinned staging ring of the file loader (allocated on first use)
+    static constexpr int kStagingBuffers = 3;
+    char* h_staging[kStagingBuffers] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_staging[kStagingBuffers] = {nullptr, nullptr, nullptr};
+    uint64_t staging_bytes = 0;
     bool measurement_staged = false, guess_staged = false;
     int launches = 0;
     sart_stats stats{};
@@ -264,7 +273,7 @@ int plan_fused(sart_engine* e) {
     }
     if (!S) return unavailable("a row panel does not fit twice into shared memory");
     // long rows only, unless forced: short rows make the per-row exchange dominate
-    if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 2048)) return SART_OK;
+    if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 1024)) return SART_OK;
 
     const int k_need = (int)ceil_div(wc, nt);
     const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need);
@@ -828,6 +837,10 @@ void free_engine(sart_engine* e) {
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (e->h_st) cudaFreeHost(e->h_st);
+    for (int k = 0; k < sart_engine::kStagingBuffers; ++k) {
+        if (e->h_staging[k]) cudaFreeHost(e->h_staging[k]);
+        if (e->ev_staging[k]) cudaEventDestroy(e->ev_staging[k]);
+    }
     cudaEvent_t evs[] = {e->ev_solve0, e->ev_solve1, e->ev_it0, e->ev_batch[0], e->ev_batch[1]};
     for (cudaEvent_t ev : evs)
         if (ev) cudaEventDestroy(ev);
@@ -1017,6 +1030,79 @@ int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->finalized = false;
     return SART_OK;
+}
+
+int sart_load_rows_file(sart_engine* e, const char* path, uint64_t file_offset, uint64_t file_ld, uint64_t local_row0,
+                        uint64_t nrows, uint64_t col0, uint64_t ncols) {
+    SART_TRY(require(e, false));
+    if (!path || local_row0 + nrows > e->P || col0 + ncols > e->V || file_ld < ncols)
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_load_rows_file: block outside the shard or file_ld < ncols");
+    if (nrows == 0 || ncols == 0) return SART_OK;
+    const int fd = ::open(path, O_RDONLY);
+    if (fd < 0) return fail(SART_ERR_INVALID_ARGUMENT, std::string("cannot open ") + path + ": " + std::strerror(errno));
+
+    // ring of pinned buffers: the read of slab k+1 (host thread, pread) overlaps the copy of slab k (DMA engine)
+    const uint64_t want = (uint64_t)std::max(1, env_int("SART_STAGING_MB", 64)) << 20;
+    const uint64_t row_bytes = ncols * sizeof(float);
+    const uint64_t slab_rows = std::max<uint64_t>(1, want / row_bytes);
+    const uint64_t need = slab_rows * row_bytes;
+    int rc = SART_OK;
+    if (e->staging_bytes < need) {
+        for (int k = 0; k < sart_engine::kStagingBuffers; ++k) {
+            if (e->h_staging[k]) cudaFreeHost(e->h_staging[k]);
+            e->h_staging[k] = nullptr;
+            if (cudaHostAlloc(reinterpret_cast<void**>(&e->h_staging[k]), need, cudaHostAllocDefault) != cudaSuccess) {
+                ::close(fd);
+                e->staging_bytes = 0;
+                return fail(SART_ERR_CUDA, "cannot allocate pinned staging memory");
+            }
+            if (!e->ev_staging[k] && cudaEventCreateWithFlags(&e->ev_staging[k], cudaEventDisableTiming) != cudaSuccess) {
+                ::close(fd);
+                return fail(SART_ERR_CUDA, "cannot create staging event");
+            }
+        }
+        e->staging_bytes = need;
+    }
+    bool in_use[sart_engine::kStagingBuffers] = {false, false, false};
+    int k = 0;
+    for (uint64_t r = 0; r < nrows && rc == SART_OK; r += slab_rows, k = (k + 1) % sart_engine::kStagingBuffers) {
+        const uint64_t n = std::min(slab_rows, nrows - r);
+        if (in_use[k] && cudaEventSynchronize(e->ev_staging[k]) != cudaSuccess) {
+            rc = fail(SART_ERR_CUDA, "staging event failed");
+            break;
+        }
+        char* dst = e->h_staging[k];
+        // rows of the block are contiguous in the file only when the block spans whole file rows
+        const bool contiguous = (ncols == file_ld);
+        const uint64_t chunks = contiguous ? 1 : n;
+        const uint64_t chunk_bytes = contiguous ? n * row_bytes : row_bytes;
+        for (uint64_t c = 0; c < chunks && rc == SART_OK; ++c) {
+            uint64_t done = 0;
+            const uint64_t off = file_offset + ((r + c) * file_ld) * sizeof(float);
+            while (done < chunk_bytes) {
+                const ssize_t got = ::pread(fd, dst + c * row_bytes + done, chunk_bytes - done, (off_t)(off + done));
+                if (got <= 0) {
+                    rc = fail(SART_ERR_INVALID_ARGUMENT, std::string("short read on ") + path +
+                                                             (got < 0 ? std::string(": ") + std::strerror(errno) : ""));
+                    break;
+                }
+                done += (uint64_t)got;
+            }
+        }
+        if (rc != SART_OK) break;
+        if (cudaMemcpy2DAsync(e->dH + (local_row0 + r) * e->ld + col0, e->ld * sizeof(float), dst, row_bytes, row_bytes, n,
+                              cudaMemcpyHostToDevice, e->stream) != cudaSuccess ||
+            cudaEventRecord(e->ev_staging[k], e->stream) != cudaSuccess) {
+            rc = fail(SART_ERR_CUDA, std::string("copy into the shard failed: ") + cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+        in_use[k] = true;
+    }
+    ::close(fd);
+    cudaError_t err = cudaStreamSynchronize(e->stream);
+    if (rc == SART_OK && err != cudaSuccess) rc = fail(SART_ERR_CUDA, std::string("CUDA error: ") + cudaGetErrorString(err));
+    e->finalized = false;
+    return rc;
 }
 
 int sart_fill_synthetic(sart_engine* e, uint64_t seed) {

@@ -338,3 +338,37 @@ def test_engine_matches_the_reference_gpu_solver(sart, restatement):
             eng.finalize()
             x = eng.solve(g)[0]
         assert rel_l2(x, x_ref) <= TOL
+
+
+def test_file_loader_streams_blocks_through_pinned_staging(sart, tmp_path, monkeypatch):
+    """Row blocks x column segments from raw files (what per-camera x per-segment files are) land exactly where
+    sart_upload_rows would put them; a 1 MB staging size forces many slabs and the ring to wrap."""
+    monkeypatch.setenv("SART_STAGING_MB", "1")
+    rng = np.random.default_rng(5)
+    P, V = 1500, 777
+    H = rng.random((P, V), dtype=np.float32)
+    header = 24
+    seg = [(0, 300), (300, 777)]           # two voxel segments
+    cams = [(0, 900), (900, 1500)]         # two cameras
+    with sart.Engine(P, V, device=0) as eng:
+        for ci, (r0, r1) in enumerate(cams):
+            for si, (c0, c1) in enumerate(seg):
+                path = tmp_path / f"cam{ci}_seg{si}.bin"
+                with open(path, "wb") as f:
+                    f.write(b"\0" * header)
+                    f.write(np.ascontiguousarray(H[r0:r1, c0:c1]).tobytes())
+                eng.load_rows_file(path, header, c1 - c0, r0, r1 - r0, c0, c1 - c0)
+        np.testing.assert_array_equal(eng.download_rows(), H)
+        # a block that is a column window of wider file rows (file_ld > ncols)
+        whole = tmp_path / "whole.bin"
+        H2 = rng.random((P, V), dtype=np.float32)
+        whole.write_bytes(H2.tobytes())
+        eng.load_rows_file(whole, 0, V, 0, P, 0, V)
+        eng.load_rows_file(whole, 100 * 4, V, 10, 50, 100, 200)  # rows 0..49 of the file, columns 100..299 -> rows 10..59
+        expect = H2.copy()
+        expect[10:60, 100:300] = H2[0:50, 100:300]
+        np.testing.assert_array_equal(eng.download_rows(), expect)
+        with pytest.raises(sart.SartError):
+            eng.load_rows_file(tmp_path / "missing.bin", 0, V, 0, P, 0, V)
+        with pytest.raises(sart.SartError):
+            eng.load_rows_file(whole, 8, V, 0, P, 0, V)  # would run past the end of the file
