@@ -229,6 +229,7 @@ def run_engine_arm(args, cp):
     sampler = ClockSampler(device) if cp.rank == 0 else None  # started before the warm-up so samples flow by t0
     for _ in range(args.warmup):
         resident_step()
+    torch.cuda.synchronize()
     cp.barrier()
     w0 = time.perf_counter()
     dev_ms, launches, fp_ms, bp_ms, fu_ms, fp_n, bp_n, fu_n = 0.0, 0, 0.0, 0.0, 0.0, 0, 0, 0
@@ -242,6 +243,7 @@ def run_engine_arm(args, cp):
         fp_n += s.fp_launches
         bp_n += s.bp_launches
         fu_n += s.fused_launches
+    torch.cuda.synchronize()  # (every step already ended with an event sync on the engine's own stream)
     sweep_mode = {1: "split", 2: "fused"}.get(s.sweep_mode, "?")
     exchange_mode = {0: "none", 1: "nccl", 2: "peer-memory kernel"}.get(s.exchange_mode, "?")
     cp.barrier()

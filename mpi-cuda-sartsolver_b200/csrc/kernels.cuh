@@ -510,22 +510,36 @@ __global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs 
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void frame_stats_kernel(const double* __restrict__ g, uint64_t P, FrameScalars* fs) {
     __shared__ double smax[32], ssum[32];
-    double mx = -INFINITY, sm = 0.0;
-    for (uint64_t i = threadIdx.x; i < P; i += blockDim.x) {
-        const double v = g[i];
-        mx = fmax(mx, v);
-        sm += (v > 0) ? v * v : 0.0;
+    // four independent accumulators per thread: the loop is latency-bound (one CTA, fixed summation order)
+    double mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, sm[4] = {0.0, 0.0, 0.0, 0.0};
+    const uint64_t stride = blockDim.x;
+    uint64_t i = threadIdx.x;
+    for (; i + 3 * stride < P; i += 4 * stride) {
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = g[i + u * stride];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            mx[u] = fmax(mx[u], v[u]);
+            sm[u] += (v[u] > 0) ? v[u] * v[u] : 0.0;
+        }
     }
-    mx = warp_max(mx);
-    sm = warp_sum(sm);
+    for (; i < P; i += stride) {
+        const double v = g[i];
+        mx[0] = fmax(mx[0], v);
+        sm[0] += (v > 0) ? v * v : 0.0;
+    }
+    double m = warp_max(fmax(fmax(mx[0], mx[1]), fmax(mx[2], mx[3])));
+    double s = warp_sum((sm[0] + sm[1]) + (sm[2] + sm[3]));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     if (lane == 0) {
-        smax[warp] = mx;
-        ssum[warp] = sm;
+        smax[warp] = m;
+        ssum[warp] = s;
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        double m = smax[0], s = ssum[0];
+        m = smax[0];
+        s = ssum[0];
         for (int k = 1; k < nw; ++k) {
             m = fmax(m, smax[k]);
             s += ssum[k];

@@ -372,3 +372,32 @@ def test_file_loader_streams_blocks_through_pinned_staging(sart, tmp_path, monke
             eng.load_rows_file(tmp_path / "missing.bin", 0, V, 0, P, 0, V)
         with pytest.raises(sart.SartError):
             eng.load_rows_file(whole, 8, V, 0, P, 0, V)  # would run past the end of the file
+
+
+def test_call_order_and_argument_errors_are_reported_not_fatal(sart):
+    """Every misuse comes back as an error code + message (the reference would print and exit(1))."""
+    import ctypes as C
+    with sart.Engine(64, 32, device=0) as eng:
+        with pytest.raises(sart.SartError) as ei:
+            eng.solve(np.ones(64))  # before sart_finalize
+        assert ei.value.code == sart.ERR_STATE
+        with pytest.raises(sart.SartError):
+            eng.upload_rows(np.zeros((65, 32), np.float32))  # more rows than the shard has
+        eng.set_laplacian(np.array([32 * 32 + 1], np.uint64), np.array([1.0], np.float32))  # row index 32 of 32 voxels
+        with pytest.raises(sart.SartError) as ei:
+            eng.finalize()
+        assert ei.value.code == sart.ERR_INVALID_ARGUMENT and "out of range" in ei.value.message
+        eng.set_laplacian(np.zeros(0, np.uint64), np.zeros(0, np.float32))
+        eng.upload_rows(np.ones((64, 32), np.float32))
+        eng.finalize()
+        with pytest.raises(sart.SartError):
+            eng.solve_resident(False)  # nothing staged
+        with pytest.raises(ValueError):
+            eng.solve(np.ones(63))
+        x, st, it = eng.solve(np.zeros(64))  # an all-dark frame: m2 = 0, the metric is NaN, runs to max_iterations
+        assert st == sart.MAX_ITERATIONS_EXCEEDED and it == 2000 and np.all(x == 0)
+    with pytest.raises(sart.SartError):
+        sart.Engine(64, 32, device=99)
+    with pytest.raises(sart.SartError) as ei:
+        sart.Engine(64, 300000, device=0, sweep_mode=FUSED)  # wider than 16 CTAs can hold
+    assert "not available" in ei.value.message
