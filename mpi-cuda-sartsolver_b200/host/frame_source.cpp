@@ -9,13 +9,36 @@ namespace {
 constexpr double kTimeEpsilon = 1.e-10;  // TIME_EPSILON of the reference (source/include/image.hpp)
 }
 
-CompositeFrames::CompositeFrames(std::vector<rawfiles::ImgHeader> imgs, const std::vector<std::array<double, 4>>& time_intervals)
-    : images(std::move(imgs)) {
+CameraSeries camera_from_raw(const rawfiles::ImgHeader& h) {
+    CameraSeries c;
+    c.name = h.path;
+    c.pixel_offset = h.pixel_offset;
+    c.npixel = h.npixel;
+    c.time = h.time;
+    const std::string path = h.path;
+    const uint64_t data_offset = h.data_offset(), npixel = h.npixel;
+    c.read = [path, data_offset, npixel](size_t index, uint64_t first, uint64_t count, double* out, std::string& error) {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) {
+            error = "cannot open " + path;
+            return false;
+        }
+        const uint64_t pos = data_offset + (index * npixel + first) * 8;
+        const bool ok = fseeko(f, (off_t)pos, SEEK_SET) == 0 && rawfiles::read_exact(f, out, count * 8);
+        std::fclose(f);
+        if (!ok) error = "short read on " + path;
+        return ok;
+    };
+    return c;
+}
+
+CompositeFrames::CompositeFrames(std::vector<CameraSeries> cams, const std::vector<std::array<double, 4>>& time_intervals)
+    : images(std::move(cams)) {
     std::sort(images.begin(), images.end(), [](const auto& a, const auto& b) { return a.pixel_offset < b.pixel_offset; });
     for (const auto& im : images) {
-        if (im.pixel_offset != npix) throw std::runtime_error("Image files do not tile the pixel range: " + im.path);
+        if (im.pixel_offset != npix) throw std::runtime_error("Image files do not tile the pixel range: " + im.name);
         if (!std::is_sorted(im.time.begin(), im.time.end()))
-            throw std::runtime_error("Image frames are not sorted by time in " + im.path + ".");
+            throw std::runtime_error("Image frames are not sorted by time in " + im.name + ".");
         npix += im.npixel;
     }
     // source/image.cpp:83-98: per interval, the frames of every camera with start <= t <= stop
@@ -102,18 +125,7 @@ bool CompositeFrames::read(size_t k, uint64_t offset, uint64_t count, std::vecto
         const auto& im = images[cam];
         const uint64_t lo = std::max(offset, im.pixel_offset), hi = std::min(offset + count, im.pixel_offset + im.npixel);
         if (lo >= hi) continue;
-        FILE* f = std::fopen(im.path.c_str(), "rb");
-        if (!f) {
-            error = "cannot open " + im.path;
-            return false;
-        }
-        const uint64_t pos = im.data_offset() + (frame_indices[k][cam] * im.npixel + (lo - im.pixel_offset)) * 8;
-        const bool ok = std::fseek(f, (long)pos, SEEK_SET) == 0 && rawfiles::read_exact(f, out.data() + (lo - offset), (hi - lo) * 8);
-        std::fclose(f);
-        if (!ok) {
-            error = "short read on " + im.path;
-            return false;
-        }
+        if (!im.read(frame_indices[k][cam], lo - im.pixel_offset, hi - lo, out.data() + (lo - offset), error)) return false;
     }
     return true;
 }

@@ -9,12 +9,26 @@
 #include <string>
 #include <vector>
 
+#include <functional>
+
 #include "raw_files.hpp"
+
+// One camera's image series: where its pixels sit in the composite frame, its timeline, and how to read pixels
+// [first, first + count) of its frame `index` (the container -- flat file or HDF5 -- is the caller's business).
+struct CameraSeries {
+    std::string name;
+    uint64_t pixel_offset = 0, npixel = 0;
+    std::vector<double> time;
+    std::function<bool(size_t index, uint64_t first, uint64_t count, double* out, std::string& error)> read;
+};
+
+CameraSeries camera_from_raw(const rawfiles::ImgHeader& header);
 
 class CompositeFrames {
 public:
-    // images: one per camera, ordered by pixel_offset; their pixel ranges must tile [0, npixel)
-    CompositeFrames(std::vector<rawfiles::ImgHeader> images, const std::vector<std::array<double, 4>>& time_intervals);
+    // cameras in composite order (the reference: lexicographic camera name); their pixel ranges must tile [0, npixel)
+    CompositeFrames(std::vector<CameraSeries> cameras, const std::vector<std::array<double, 4>>& time_intervals);
+    const std::vector<CameraSeries>& cameras() const { return images; }
 
     size_t size() const { return frame_indices.size(); }
     double frame_time(size_t k) const { return time[k]; }
@@ -29,7 +43,7 @@ public:
     void add_interval(const std::vector<std::vector<std::pair<double, size_t>>>& timepairs, double step, double threshold);
 
 private:
-    std::vector<rawfiles::ImgHeader> images;
+    std::vector<CameraSeries> images;
     uint64_t npix = 0;
     std::vector<std::vector<size_t>> frame_indices;  // [composite frame][camera] -> frame index in that camera's file
     std::vector<std::vector<double>> camera_time;

@@ -16,6 +16,7 @@
 #include "../../include/sart_b200.h"
 #include "arguments_b200.hpp"
 #include "frame_source.hpp"
+#include "h5_schema.hpp"
 #include "raw_files.hpp"
 
 namespace {
@@ -38,37 +39,57 @@ int main(int argc, char* argv[]) {
     if (!parse_time_intervals(config.time_range, time_intervals, error)) die(error);
     if (config.use_cpu) die("This build has no CPU solver (--use_cpu): the engine runs on the GPU only.");
 
-    // source/hdf5files.cpp:20-43: every input is either a ray-transfer file or an image file
-    std::vector<rawfiles::RtmHeader> matrix_files;
-    std::vector<rawfiles::ImgHeader> image_files;
-    for (const auto& path : config.input_files) {
-        const std::string magic = rawfiles::file_magic(path);
-        if (magic == rawfiles::kRtmMagic) {
-            rawfiles::RtmHeader h;
-            if (!rawfiles::read_rtm_header(path, h)) die("Unable to read " + path + ".");
-            matrix_files.push_back(h);
-        } else if (magic == rawfiles::kImgMagic) {
-            rawfiles::ImgHeader h;
-            if (!rawfiles::read_img_header(path, h)) die("Unable to read " + path + ".");
-            image_files.push_back(h);
-        } else {
-            die("File " + path + " is neither a ray-transfer matrix nor an image file.");
-        }
-    }
-    if (matrix_files.empty() || image_files.empty()) die("At least one ray-transfer file and one image file are required.");
+    // Inputs are either all HDF5 files in the reference's schemas (read with h5lite) or all flat stand-in files.
+    const bool hdf5 = h5schema::is_hdf5(config.input_files.front());
+    for (const auto& path : config.input_files)
+        if (h5schema::is_hdf5(path) != hdf5) die("HDF5 and flat input files cannot be mixed.");
 
-    // source/hdf5files.cpp:349-389: total size from the files; the blocks must cover it exactly once
-    uint64_t npixel = 0, nvoxel = 0, covered = 0;
-    for (const auto& h : matrix_files) {
-        npixel = std::max(npixel, h.pixel_offset + h.npixel);
-        nvoxel = std::max(nvoxel, h.voxel_offset + h.nvoxel);
-        covered += h.npixel * h.nvoxel;
+    std::vector<rawfiles::RtmHeader> matrix_files;
+    h5schema::Problem h5;
+    std::vector<CameraSeries> cameras;
+    std::vector<std::string> camera_names;
+    uint64_t npixel = 0, nvoxel = 0;
+    if (hdf5) {
+        try {
+            h5 = h5schema::open_problem(config.input_files, config.raytransfer_name, config.wavelength_threshold);
+        } catch (const std::exception& err) {
+            die(err.what());
+        }
+        npixel = h5.npixel;
+        nvoxel = h5.nvoxel;
+        cameras = h5.cameras;
+        camera_names = h5.camera_names;
+    } else {
+        // source/hdf5files.cpp:20-43: every input is either a ray-transfer file or an image file
+        for (const auto& path : config.input_files) {
+            const std::string magic = rawfiles::file_magic(path);
+            if (magic == rawfiles::kRtmMagic) {
+                rawfiles::RtmHeader h;
+                if (!rawfiles::read_rtm_header(path, h)) die("Unable to read " + path + ".");
+                matrix_files.push_back(h);
+            } else if (magic == rawfiles::kImgMagic) {
+                rawfiles::ImgHeader h;
+                if (!rawfiles::read_img_header(path, h)) die("Unable to read " + path + ".");
+                cameras.push_back(camera_from_raw(h));
+                camera_names.push_back("camera" + std::to_string(camera_names.size()));
+            } else {
+                die("File " + path + " is neither a ray-transfer matrix nor an image file.");
+            }
+        }
+        if (matrix_files.empty() || cameras.empty()) die("At least one ray-transfer file and one image file are required.");
+        // source/hdf5files.cpp:349-389: total size from the files; the blocks must cover it exactly once
+        uint64_t covered = 0;
+        for (const auto& h : matrix_files) {
+            npixel = std::max(npixel, h.pixel_offset + h.npixel);
+            nvoxel = std::max(nvoxel, h.voxel_offset + h.nvoxel);
+            covered += h.npixel * h.nvoxel;
+        }
+        if (covered != npixel * nvoxel) die("Ray-transfer files do not tile the matrix exactly once.");
     }
-    if (covered != npixel * nvoxel) die("Ray-transfer files do not tile the matrix exactly once.");
 
     CompositeFrames* frames = nullptr;
     try {
-        frames = new CompositeFrames(image_files, time_intervals);
+        frames = new CompositeFrames(cameras, time_intervals);
     } catch (const std::runtime_error& err) {
         die(err.what());
     }
@@ -95,6 +116,29 @@ int main(int argc, char* argv[]) {
 
     // source/raytransfer.cpp:27-127 without the host copy: each file block's rows that fall into this rank's range
     const auto t_load = std::chrono::steady_clock::now();
+    for (const auto& b : h5.blocks) {
+        const uint64_t lo = std::max(b.pixel_offset, offset_pixel), hi = std::min(b.pixel_offset + b.npixel, offset_pixel + npixel_local);
+        if (lo >= hi) continue;
+        try {
+            h5lite::File f(b.path);
+            const uint64_t data_offset = b.sparse ? UINT64_MAX : f.contiguous_offset(b.dataset);
+            if (data_offset != UINT64_MAX) {
+                // contiguous, unfiltered dataset: stream it straight from the file (what H5Dget_offset allows)
+                must(sart_load_rows_file(engine, b.path.c_str(), data_offset + (lo - b.pixel_offset) * b.nvoxel * sizeof(float), b.nvoxel,
+                                         lo - offset_pixel, hi - lo, b.voxel_offset, b.nvoxel));
+            } else {
+                // chunked / compressed / sparse: decode slabs of rows on the host
+                const uint64_t slab = std::max<uint64_t>(1, (64ull << 20) / (b.nvoxel * sizeof(float)));
+                for (uint64_t r = lo; r < hi; r += slab) {
+                    const uint64_t n = std::min(slab, hi - r);
+                    const std::vector<float> rows = h5schema::read_block_rows(b, r - b.pixel_offset, n);
+                    must(sart_upload_rows(engine, r - offset_pixel, n, b.voxel_offset, b.nvoxel, rows.data(), b.nvoxel));
+                }
+            }
+        } catch (const std::exception& err) {
+            die(err.what());
+        }
+    }
     for (const auto& h : matrix_files) {
         const uint64_t lo = std::max(h.pixel_offset, offset_pixel), hi = std::min(h.pixel_offset + h.npixel, offset_pixel + npixel_local);
         if (lo >= hi) continue;
@@ -107,18 +151,36 @@ int main(int argc, char* argv[]) {
         uint64_t lap_nvoxel = 0;
         std::vector<uint64_t> index;
         std::vector<float> value;
-        if (!rawfiles::read_laplacian(config.laplacian_file, lap_nvoxel, index, value)) die("Unable to read " + config.laplacian_file + ".");
+        if (h5schema::is_hdf5(config.laplacian_file)) {
+            try {
+                h5schema::read_laplacian(config.laplacian_file, nvoxel, index, value);
+                lap_nvoxel = nvoxel;
+            } catch (const std::exception& err) {
+                die(err.what());
+            }
+        } else if (!rawfiles::read_laplacian(config.laplacian_file, lap_nvoxel, index, value)) {
+            die("Unable to read " + config.laplacian_file + ".");
+        }
         if (lap_nvoxel != nvoxel) die("Laplacian and ray-transfer matrices have different number of voxels.");  // laplacian.cpp:46-49
         must(sart_set_laplacian_coo(engine, index.data(), value.data(), index.size()));
     }
     must(sart_finalize(engine));
     std::cout << "Matrix " << npixel << " x " << nvoxel << " loaded in: " << load_ms.count() << " ms" << std::endl;
 
-    FILE* out = std::fopen(config.output_file.c_str(), "wb");
-    if (!out) die("Unable to open " + config.output_file + ".");
-    const uint64_t head[2] = {nvoxel, (uint64_t)frames->size()};
-    std::fwrite(rawfiles::kSolMagic, 1, 8, out);
-    std::fwrite(head, sizeof(uint64_t), 2, out);
+    // flat output: one record per frame as it is solved; HDF5 output: the reference's solution file, written at the end
+    const bool h5_out = config.output_file.size() > 3 && (config.output_file.rfind(".h5") == config.output_file.size() - 3 ||
+                                                          config.output_file.rfind(".hdf5") == config.output_file.size() - 5);
+    FILE* out = nullptr;
+    if (!h5_out) {
+        out = std::fopen(config.output_file.c_str(), "wb");
+        if (!out) die("Unable to open " + config.output_file + ".");
+        const uint64_t head[2] = {nvoxel, (uint64_t)frames->size()};
+        std::fwrite(rawfiles::kSolMagic, 1, 8, out);
+        std::fwrite(head, sizeof(uint64_t), 2, out);
+    }
+    std::vector<double> all_values, all_time;
+    std::vector<std::vector<double>> all_camera_time;
+    std::vector<int32_t> all_status, all_iterations;
 
     // source/main.cpp:127-140
     std::vector<double> solution_vec, frame;
@@ -132,13 +194,30 @@ int main(int argc, char* argv[]) {
         const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
         std::cout << "Processed in: " << duration.count() << " ms" << std::endl;
         const double t = frames->frame_time(k);
-        std::fwrite(&t, sizeof(double), 1, out);
-        std::fwrite(&status, sizeof(int32_t), 1, out);
-        std::fwrite(&iterations, sizeof(int32_t), 1, out);
-        std::fwrite(solution_vec.data(), sizeof(double), nvoxel, out);
+        if (h5_out) {
+            all_values.insert(all_values.end(), solution_vec.begin(), solution_vec.end());
+            all_time.push_back(t);
+            all_camera_time.push_back(frames->camera_frame_time(k));
+            all_status.push_back(status);
+            all_iterations.push_back(iterations);
+        } else {
+            std::fwrite(&t, sizeof(double), 1, out);
+            std::fwrite(&status, sizeof(int32_t), 1, out);
+            std::fwrite(&iterations, sizeof(int32_t), 1, out);
+            std::fwrite(solution_vec.data(), sizeof(double), nvoxel, out);
+        }
         if (config.no_guess) solution_vec.clear();
     }
-    std::fclose(out);
+    if (h5_out) {
+        try {
+            h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time, all_status,
+                                     all_iterations, h5.grid);
+        } catch (const std::exception& err) {
+            die(err.what());
+        }
+    } else {
+        std::fclose(out);
+    }
     sart_destroy(engine);
     delete frames;
     return 0;

@@ -16,14 +16,14 @@ int main(int argc, char* argv[]) {
         std::cerr << error << std::endl;
         return 1;
     }
-    std::vector<rawfiles::ImgHeader> images;
+    std::vector<CameraSeries> images;
     for (int i = 2; i < argc; ++i) {
         rawfiles::ImgHeader h;
         if (!rawfiles::read_img_header(argv[i], h)) {
             std::cerr << "Unable to read " << argv[i] << "." << std::endl;
             return 1;
         }
-        images.push_back(h);
+        images.push_back(camera_from_raw(h));
     }
     try {
         CompositeFrames frames(images, intervals);

@@ -1,0 +1,80 @@
+"""h5lite (host/h5lite.cpp), the native HDF5 subset reader/writer. Not verifiable against libhdf5 on this image; checked
+against the one third-party HDF5 file present (scipy's MATLAB v7.3 test file), against an independent pure-Python
+writer for chunked / compressed data and variable-length strings, and writer -> reader round trips. CPU only."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from tests.h5w import H5Writer, h5ls, write_chunked_h5
+
+
+def test_reads_the_third_party_file_on_the_image():
+    import scipy.io.matlab
+    hits = glob.glob(os.path.join(os.path.dirname(scipy.io.matlab.__file__), "tests", "data", "testhdf5_7.4_GLNX86.mat"))
+    if not hits:
+        pytest.skip("scipy's MATLAB v7.3 test file is not installed")
+    objs = h5ls(hits[0])  # written by MATLAB 7.4's HDF5 library in 2008: 512-byte user block, version-2 layout message
+    d = objs["testdouble"]
+    assert (d["kind"], d["class"], d["size"], d["dims"], d["layout"]) == ("dataset", "float", 8, [9, 1], 1)
+    np.testing.assert_allclose(d["values"], np.linspace(0, 2 * np.pi, 9), rtol=1e-15)
+    assert d["attributes"]["MATLAB_class"] == "double"
+    assert d["contiguous_offset"] == 4096
+
+
+def test_writer_reader_round_trip(tmp_path):
+    p = tmp_path / "rt.h5"
+    rng = np.random.default_rng(1)
+    value = rng.standard_normal((5, 37))
+    frames = rng.random((3, 4, 6))
+    w = H5Writer(p)
+    w.group("solution")
+    w.group("solution/deep")
+    w.dataset("solution/value", value)
+    w.dataset("solution/status", np.array([0, -1, 0, 0, -1], dtype=np.int32))
+    w.dataset("solution/deep/frames", frames)
+    w.dataset("solution/idx", np.array([0, 2 ** 40, 7], dtype=np.uint64))
+    w.dataset("solution/f32", value.astype(np.float32))
+    for k in range(40):  # more links than the default 8 per symbol node
+        w.dataset(f"solution/deep/d{k:02d}", np.full(3, float(k)))
+    w.attr("solution", "nvoxel", 37)
+    w.attr("solution", "beta", 0.02)
+    w.attr("solution", "name", "with_reflections")
+    w.attr("solution/value", "flag", np.int32(-7))
+    w.close()
+    o = h5ls(p)
+    np.testing.assert_array_equal(np.array(o["solution/value"]["values"]).reshape(5, 37), value)
+    np.testing.assert_array_equal(np.array(o["solution/deep/frames"]["values"]).reshape(3, 4, 6), frames)
+    assert o["solution/status"]["values"] == [0, -1, 0, 0, -1] and o["solution/status"]["signed"] == 1
+    assert o["solution/idx"]["values"] == [0, 2 ** 40, 7]
+    np.testing.assert_array_equal(np.array(o["solution/f32"]["values"], dtype=np.float32).reshape(5, 37), value.astype(np.float32))
+    assert o["solution"]["attributes"] == {"beta": 0.02, "name": "with_reflections", "nvoxel": 37}
+    assert o["solution/value"]["attributes"] == {"flag": -7}
+    assert all(o[f"solution/deep/d{k:02d}"]["values"] == [float(k)] * 3 for k in range(40))
+
+
+@pytest.mark.parametrize("deflate,shuffle,chunk", [(True, True, (16, 32)), (True, False, (7, 5)), (False, False, (64, 64)), (False, True, (10, 100))])
+def test_reads_chunked_filtered_datasets_and_vlen_strings(tmp_path, deflate, shuffle, chunk):
+    p = tmp_path / "chunked.h5"
+    a = np.random.default_rng(2).random((50, 70), dtype=np.float32)
+    write_chunked_h5(p, a, chunk, deflate=deflate, shuffle=shuffle, vlen_attr=("camera_name", "divertor_view_3"))
+    o = h5ls(p)
+    d = o["data"]
+    assert d["layout"] == 2 and d["dims"] == [50, 70] and d["contiguous_offset"] == -1
+    assert d["filters"] == ([2] if shuffle else []) + ([1] if deflate else [])
+    np.testing.assert_array_equal(np.array(d["values"], dtype=np.float32).reshape(50, 70), a)
+    assert o["/"]["attributes"]["camera_name"] == "divertor_view_3"  # variable-length string from the global heap
+
+
+def test_rejects_what_it_cannot_read(tmp_path):
+    import subprocess
+    from tests.h5w import HOST
+    p = tmp_path / "not.h5"
+    p.write_bytes(b"definitely not hdf5" * 10)
+    out = subprocess.run([os.path.join(HOST, "sart_b200_h5ls"), str(p)], capture_output=True, text=True)
+    assert out.returncode == 1 and "is not an HDF5 file" in out.stderr
+    v2 = bytearray(bytes([0x89]) + b"HDF\r\n\x1a\n" + bytes([2]) + b"\0" * 100)
+    p.write_bytes(bytes(v2))
+    out = subprocess.run([os.path.join(HOST, "sart_b200_h5ls"), str(p)], capture_output=True, text=True)
+    assert out.returncode == 1 and "not supported" in out.stderr
