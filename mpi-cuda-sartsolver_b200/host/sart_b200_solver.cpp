@@ -3,10 +3,18 @@
 // order: source/hdf5files.cpp:20-43), matrix extents from the files (:349-389), frame selection and multi-camera
 // synchronisation (frame_source.cpp), Laplacian, solver set-up, frame loop with warm start / --no_guess, per-frame
 // "Processed in: ... ms", and one solution record per frame. The matrix never sits in host memory: every file block is
-// streamed into the GPU shard through sart_load_rows_file's pinned staging ring. Single process / single GPU; a multi-GPU
-// job is the same program per rank with the communicator id shipped as shown in INTEGRATION.md.
+// streamed into the GPU shard through sart_load_rows_file's pinned staging ring.
+// Several GPUs: start one process per GPU with RANK / WORLD_SIZE (torchrun style) or OMPI_COMM_WORLD_RANK / _SIZE or
+// PMI_RANK / PMI_SIZE in the environment (what mpirun / srun export); since there is no MPI library to link against on
+// this image, the 128-byte communicator id travels from rank 0 to the others through the file named by
+// SART_COMM_ID_FILE (default /tmp/sart_b200_comm_id.<MASTER_PORT or parent pid>). Every rank loads only its own rows
+// and pixels; rank 0 alone prints and writes the solution, as in the reference.
+#include <unistd.h>
+
 #include <chrono>
 #include <cstdint>
+#include <cstdlib>
+#include <thread>
 #include <cstdio>
 #include <iostream>
 #include <limits>
@@ -28,6 +36,41 @@ namespace {
 
 void must(int rc) {
     if (rc != SART_OK) die(sart_last_error());
+}
+
+int env_int(std::initializer_list<const char*> names, int dflt) {
+    for (const char* n : names)
+        if (const char* v = std::getenv(n))
+            if (*v) return std::atoi(v);
+    return dflt;
+}
+
+// rank 0 publishes the communicator id through a file (write + atomic rename), the others wait for it
+void exchange_comm_id(int rank, uint8_t id[SART_UNIQUE_ID_BYTES], std::string& path) {
+    if (const char* p = std::getenv("SART_COMM_ID_FILE")) path = p;
+    else {
+        const char* port = std::getenv("MASTER_PORT");
+        path = "/tmp/sart_b200_comm_id." + (port ? std::string(port) : std::to_string((long)getppid()));
+    }
+    if (rank == 0) {
+        must(sart_comm_unique_id(id));
+        const std::string tmp = path + ".tmp";
+        FILE* f = std::fopen(tmp.c_str(), "wb");
+        if (!f || std::fwrite(id, 1, SART_UNIQUE_ID_BYTES, f) != SART_UNIQUE_ID_BYTES) die("Unable to write " + tmp + ".");
+        std::fclose(f);
+        if (std::rename(tmp.c_str(), path.c_str()) != 0) die("Unable to publish " + path + ".");
+        return;
+    }
+    for (int waited_ms = 0; waited_ms < 120000; waited_ms += 50) {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (f) {
+            const bool ok = std::fread(id, 1, SART_UNIQUE_ID_BYTES, f) == SART_UNIQUE_ID_BYTES;
+            std::fclose(f);
+            if (ok) return;
+        }
+        std::this_thread::sleep_for(std::chrono::milliseconds(50));
+    }
+    die("Timed out waiting for the communicator id in " + path + ".");
 }
 
 }  // namespace
@@ -95,7 +138,10 @@ int main(int argc, char* argv[]) {
     }
     if (frames->npixel() != npixel) die("Ray-transfer matrices and images have different number of pixels.");
 
-    const int rank = 0, numproc = 1;
+    // source/main.cpp:63-65 (MPI_Comm_rank / MPI_Comm_size)
+    const int rank = env_int({"RANK", "OMPI_COMM_WORLD_RANK", "PMI_RANK"}, 0);
+    const int numproc = env_int({"WORLD_SIZE", "OMPI_COMM_WORLD_SIZE", "PMI_SIZE"}, 1);
+    if (numproc < 1 || rank < 0 || rank >= numproc) die("Inconsistent rank / world size in the environment.");
     sart_config cfg;
     must(sart_config_default(&cfg));
     cfg.npixel = npixel;
@@ -109,8 +155,16 @@ int main(int argc, char* argv[]) {
     cfg.beta_laplace = config.beta_laplace;
     cfg.relaxation = config.relaxation;
     cfg.max_iterations = config.max_iterations;
+    cfg.device = env_int({"LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK"}, -1);
     sart_engine* engine = nullptr;
     must(sart_create(&cfg, &engine));
+    std::string id_file;
+    if (numproc > 1) {
+        uint8_t id[SART_UNIQUE_ID_BYTES];
+        exchange_comm_id(rank, id, id_file);
+        must(sart_comm_init(engine, id));
+        if (rank == 0) std::remove(id_file.c_str());  // every rank has joined once sart_comm_init returns
+    }
     uint64_t offset_pixel = 0, npixel_local = 0;
     must(sart_shard_range(npixel, numproc, rank, &offset_pixel, &npixel_local));
 
@@ -165,13 +219,13 @@ int main(int argc, char* argv[]) {
         must(sart_set_laplacian_coo(engine, index.data(), value.data(), index.size()));
     }
     must(sart_finalize(engine));
-    std::cout << "Matrix " << npixel << " x " << nvoxel << " loaded in: " << load_ms.count() << " ms" << std::endl;
+    if (rank == 0) std::cout << "Matrix " << npixel << " x " << nvoxel << " loaded in: " << load_ms.count() << " ms" << std::endl;
 
     // flat output: one record per frame as it is solved; HDF5 output: the reference's solution file, written at the end
     const bool h5_out = config.output_file.size() > 3 && (config.output_file.rfind(".h5") == config.output_file.size() - 3 ||
                                                           config.output_file.rfind(".hdf5") == config.output_file.size() - 5);
     FILE* out = nullptr;
-    if (!h5_out) {
+    if (!h5_out && rank == 0) {
         out = std::fopen(config.output_file.c_str(), "wb");
         if (!out) die("Unable to open " + config.output_file + ".");
         const uint64_t head[2] = {nvoxel, (uint64_t)frames->size()};
@@ -192,9 +246,11 @@ int main(int argc, char* argv[]) {
         int32_t status = 0, iterations = 0;
         must(sart_solve(engine, frame.data(), solution_vec.data(), has_guess, &status, &iterations));
         const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
-        std::cout << "Processed in: " << duration.count() << " ms" << std::endl;
+        if (rank == 0) std::cout << "Processed in: " << duration.count() << " ms" << std::endl;
         const double t = frames->frame_time(k);
-        if (h5_out) {
+        if (rank != 0) {
+            // source/main.cpp:134: only the root stores solutions
+        } else if (h5_out) {
             all_values.insert(all_values.end(), solution_vec.begin(), solution_vec.end());
             all_time.push_back(t);
             all_camera_time.push_back(frames->camera_frame_time(k));
@@ -208,14 +264,14 @@ int main(int argc, char* argv[]) {
         }
         if (config.no_guess) solution_vec.clear();
     }
-    if (h5_out) {
+    if (h5_out && rank == 0) {
         try {
             h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time, all_status,
                                      all_iterations, h5.grid);
         } catch (const std::exception& err) {
             die(err.what());
         }
-    } else {
+    } else if (out) {
         std::fclose(out);
     }
     sart_destroy(engine);
