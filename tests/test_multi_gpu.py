@@ -51,3 +51,46 @@ def test_sharded_solve_matches_oracle(world):
             else:
                 assert c["exchange"] == 1, (name, c)
         assert len(hashes) == 1, f"{name}: ranks ended with different solutions"
+
+
+def test_cpp_solver_driver_on_two_gpus(tmp_path):
+    """The C++ driver as two processes (rank / world size from the environment, communicator id through a file), each
+    loading its own rows of HDF5 inputs, against the golden vectors of the reference."""
+    if _gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    from oracle.pyoracle import Restatement
+    from tests.cases import build_case, rel_l2
+    from tests.h5w import h5ls, write_laplacian_h5
+    from tests.test_solver_cli_gpu import EXE, _write_hdf5_inputs
+    name = "series_warm4"
+    case = build_case(name, Restatement())
+    golden = np.load(os.path.join(ROOT, "tests", "golden", "golden_v1.npz"))
+    kw = case["kw"]
+    files, times = _write_hdf5_inputs(tmp_path, case)
+    V = case["H"].shape[1]
+    lap = tmp_path / "laplacian.h5"
+    write_laplacian_h5(lap, case["lap"][0], case["lap"][1], V)
+    out_path = tmp_path / "solution.h5"
+    argv = [EXE, "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]), "-l", str(lap),
+            "-b", str(kw.get("beta_laplace", 2e-2)), *files]
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank),
+                   SART_COMM_ID_FILE=str(tmp_path / "comm_id"))
+        procs.append(subprocess.Popen(argv, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=600) for p in procs]
+    for p, (so, se) in zip(procs, outs):
+        assert p.returncode == 0, se[-2000:]
+    assert outs[0][0].count("Processed in:") == 4 and outs[1][0].count("Processed in:") == 0
+    o = h5ls(out_path)
+    x = np.array(o["solution/value"]["values"]).reshape(4, V)
+    its = o["solution/iterations"]["values"]
+    git = golden[name + "/iterations"]
+    same = True
+    for f in range(4):
+        assert abs(its[f] - git[f]) <= 1
+        same = same and its[f] == git[f]
+        if same:
+            assert rel_l2(x[f], golden[name + "/x"][f]) <= 1e-5
