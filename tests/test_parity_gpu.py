@@ -401,3 +401,47 @@ def test_call_order_and_argument_errors_are_reported_not_fatal(sart):
     with pytest.raises(sart.SartError) as ei:
         sart.Engine(64, 300000, device=0, sweep_mode=FUSED)  # wider than 16 CTAs can hold
     assert "not available" in ei.value.message
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_randomised_problems_against_the_oracle(seed, sart, restatement):
+    """Shapes, thresholds, masks, relaxation, regularisation, solver kind, sweep kind, semantics and warm start drawn at
+    random (reproducibly): the engine must follow the oracle on every combination."""
+    rng = np.random.default_rng(1000 + seed)
+    syn = load_synthetic()
+    P = int(rng.integers(1, 700))
+    V = int(rng.choice([1, 3, 4, 5, 31, 32, 33, 100, 255, 256, 257, 1000, 1025, 2500]))
+    H = restatement.fill_synthetic(P, V, int(rng.integers(1, 10 ** 6)))
+    if rng.random() < 0.5 and P > 4:
+        H[rng.random(P) < 0.1] = 0                       # rays that see nothing
+    if rng.random() < 0.5 and V > 4:
+        H[:, rng.random(V) < 0.1] = 0                    # voxels nobody sees
+    if rng.random() < 0.3:
+        H[rng.random(P) < 0.2] *= 1e-7                   # rows below the ray-length threshold
+    x_true = syn.emission_profile(V) * float(rng.choice([1e-3, 1.0, 1e4]))
+    g = restatement.forward(H, x_true)
+    if rng.random() < 0.5:
+        g[rng.random(P) < 0.15] = -1.0                   # saturated pixels
+    kw = dict(
+        ray_density_threshold=float(rng.choice([1e-6, 1e-3])), ray_length_threshold=float(rng.choice([1e-6, 1e-4])),
+        relaxation=float(rng.choice([1.0, 0.7, 0.25])), beta_laplace=float(rng.choice([0.0, 1e-2, 5e-2])),
+        max_iterations=int(rng.integers(1, 25)), logarithmic=bool(rng.random() < 0.35))
+    gpu_sem = bool(rng.random() < 0.3)
+    lap = syn.laplacian_coo(V) if rng.random() < 0.6 else None
+    x0 = None
+    if rng.random() < 0.4:
+        x0 = x_true * rng.uniform(0.5, 1.5, V) + 1e-3 * x_true.max()
+    mode = int(rng.choice([SPLIT, FUSED]))
+    x_ref, st_ref, it_ref = restatement.solve(H, g, x0=x0, lap=lap, fixed_iterations=True, gpu_semantics=gpu_sem, **kw)
+    with sart.Engine(P, V, device=0, fixed_iterations=True, sweep_mode=mode,
+                     semantics=sart.SEMANTICS_GPU if gpu_sem else sart.SEMANTICS_CPU, **kw) as eng:
+        eng.upload_rows(H)
+        if lap is not None:
+            eng.set_laplacian(*lap)
+        eng.finalize()
+        x, st, it = eng.solve(g, x0)
+    assert (st, it) == (st_ref, it_ref)
+    if np.all(np.isfinite(x_ref)) and np.linalg.norm(x_ref) > 0:
+        assert rel_l2(x, x_ref) <= TOL, dict(P=P, V=V, mode=mode, gpu_sem=gpu_sem, **kw)
+    else:
+        np.testing.assert_array_equal(np.isfinite(x), np.isfinite(x_ref))
