@@ -243,6 +243,7 @@ def run_engine_arm(args, cp):
         fp_n += s.fp_launches
         bp_n += s.bp_launches
         fu_n += s.fused_launches
+        tail_ms = s.tail_ms_avg
     torch.cuda.synchronize()  # (every step already ended with an event sync on the engine's own stream)
     sweep_mode = {1: "split", 2: "fused"}.get(s.sweep_mode, "?")
     exchange_mode = {0: "none", 1: "nccl", 2: "peer-memory kernel"}.get(s.exchange_mode, "?")
@@ -299,6 +300,7 @@ def run_engine_arm(args, cp):
         "kernels": kern,
         "iteration_roofline_frac": (2.0 * shard_bytes * (value / 1.0) / 1e9) / peak,  # 2*bytes(A) per iteration / peak
     }
+    cp_tail = cp.max(tail_ms)
     gathered = cp.gather({"rank": cp.rank, "dev_ms": dev_ms, "dominant_gbs": kern[dom]["gbs"]})
 
     cb = None
@@ -313,7 +315,8 @@ def run_engine_arm(args, cp):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": cp.world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(args, cp.world), sweep=sweep_mode, exchange=exchange_mode), "e2e": e2e, "gpu_launches": launches,
+            "config": dict(workload_config(args, cp.world), sweep=sweep_mode, exchange=exchange_mode), "e2e": e2e,
+            "between_sweeps_us": 1e3 * cp_tail, "gpu_launches": launches,
             "roofline": roofline, "cpu_baseline": cb, "clocks": clocks,
             "wall_ms_per_step": wall_ms / args.steps, "per_rank": gathered,
             "device": {"name": info.name.decode(), "sms": info.sm_count, "l2_bytes": info.l2_bytes,

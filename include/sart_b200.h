@@ -100,6 +100,7 @@ typedef struct sart_stats {
     int32_t sweep_mode;      /* SART_SWEEP_SPLIT or SART_SWEEP_FUSED: what the engine runs */
     int32_t exchange_mode;   /* SART_EXCHANGE_*: how the per-iteration reduction over the ranks travels */
     int32_t reserved;
+    double tail_ms_avg;      /* fused sweep: mean device time between two sweeps (reduction over clusters and ranks, decision, update) */
 } sart_stats;
 
 typedef struct sart_device_info {

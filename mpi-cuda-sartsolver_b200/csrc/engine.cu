@@ -631,6 +631,7 @@ int run_solve(sart_engine* e, int has_guess) {
     e->stats.fp_launches = e->stats.bp_launches = 0;
     e->stats.fused_ms_avg = 0;
     e->stats.fused_launches = 0;
+    e->stats.tail_ms_avg = 0;
     e->stats.sweep_mode = e->fused ? SART_SWEEP_FUSED : SART_SWEEP_SPLIT;
     e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE
                              : (e->fused && e->peer_exchange) ? SART_EXCHANGE_PEER : SART_EXCHANGE_NCCL;
@@ -656,6 +657,16 @@ int run_solve(sart_engine* e, int has_guess) {
                 ++nsecond;
             }
         }
+        // what follows a fused sweep before the next one may start: reduction over clusters and ranks, decision, update
+        double tail = 0;
+        int ntail = 0;
+        for (int k = 0; e->fused && k + 1 < nsweeps && k + 1 < e->cfg.max_iterations; ++k) {
+            float a = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][3], e->ev_prof[k + 1][2]));
+            tail += a;
+            ++ntail;
+        }
+        e->stats.tail_ms_avg = ntail ? tail / ntail : 0;
         e->stats.fp_ms_avg = nfp ? fp / nfp : 0;
         e->stats.fp_launches = nfp;
         if (e->fused) {

@@ -14,5 +14,6 @@ for line in sys.stdin:
     for name, v in k.items():
         if v["launches"]:
             parts.append(f"{name}: {v['ms']:.3f} ms x{v['launches']} alg {v['gbs']:.0f} GB/s hbm {v['hbm_gbs']:.0f} GB/s share {v['share_of_step']:.3f}")
+    parts.append(f"between_sweeps={d.get('between_sweeps_us', 0):.1f} us")
     parts.append(f"clocks={d.get('clocks')}")
     print(" | ".join(parts))
