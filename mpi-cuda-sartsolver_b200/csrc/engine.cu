@@ -198,7 +198,7 @@ int plan_launches(sart_engine* e) {
 
     e->fp_rows = fv.rows;
     e->fp_nrg = (uint32_t)ceil_div(e->P, fv.rows);
-    const int fp_ctas_per_sm = env_int("SART_FP_CTAS_PER_SM", fp_occ);
+    const int fp_ctas_per_sm = std::min(env_int("SART_FP_CTAS_PER_SM", fp_occ), 32);  // d_f2part holds 32 per SM
     e->fp_grid = (uint32_t)std::min<uint64_t>(e->fp_nrg, (uint64_t)e->sm_count * std::max(fp_ctas_per_sm, 1));
 
     // back projection: one wave of (panels x slabs) CTAs, slabs a multiple of 32 rows
