@@ -143,7 +143,7 @@ int sart_upload_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, uint64
                      const float* src, uint64_t src_ld);
 /* The same from a file, without a host-resident copy of the matrix: the block rows [local_row0, +nrows) x columns
  * [col0, +ncols) is streamed from a raw little-endian fp32 array (row-major, file_ld floats per row, first element at
- * byte file_offset of `path`) through a ring of three pinned staging buffers (SART_STAGING_MB each, default 64): the
+ * byte file_offset of `path`) through a ring of three pinned staging buffers (SART_STAGING_MB each, default 16): the
  * pread of slab k+1 overlaps the asynchronous copy of slab k, and host memory stays O(staging) however large the shard
  * is (the reference holds the whole rank-local matrix in host RAM: source/include/raytransfer.hpp:20, and copies it in
  * one blocking cudaMemcpy: source/sartsolver_cuda.cpp:104-106). Returns when the block is on the device. */

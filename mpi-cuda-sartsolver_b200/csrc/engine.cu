@@ -1053,7 +1053,7 @@ int sart_load_rows_file(sart_engine* e, const char* path, uint64_t file_offset, 
     if (fd < 0) return fail(SART_ERR_INVALID_ARGUMENT, std::string("cannot open ") + path + ": " + std::strerror(errno));
 
     // ring of pinned buffers: the read of slab k+1 (host thread, pread) overlaps the copy of slab k (DMA engine)
-    const uint64_t want = (uint64_t)std::max(1, env_int("SART_STAGING_MB", 64)) << 20;
+    const uint64_t want = (uint64_t)std::max(1, env_int("SART_STAGING_MB", 16)) << 20;
     const uint64_t row_bytes = ncols * sizeof(float);
     const uint64_t slab_rows = std::max<uint64_t>(1, want / row_bytes);
     const uint64_t need = slab_rows * row_bytes;

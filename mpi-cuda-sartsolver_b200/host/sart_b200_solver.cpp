@@ -263,6 +263,16 @@ int main(int argc, char* argv[]) {
             std::fwrite(solution_vec.data(), sizeof(double), nvoxel, out);
         }
         if (config.no_guess) solution_vec.clear();
+        // source/solution.cpp:55, 167-180: the reference appends to the file every max_cached_solutions frames so that a
+        // long run leaves its results behind if it dies; with a write-once container the file is rewritten instead
+        if (h5_out && rank == 0 && (k + 1) % (size_t)config.max_cached_solutions == 0 && k + 1 < frames->size()) {
+            try {
+                h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time,
+                                         all_status, all_iterations, h5.grid);
+            } catch (const std::exception& err) {
+                die(err.what());
+            }
+        }
     }
     if (h5_out && rank == 0) {
         try {

@@ -125,7 +125,7 @@ def test_solver_cli_on_hdf5_files_matches_golden(name, restatement, golden, tmp_
         lap = tmp_path / "laplacian.h5"
         write_laplacian_h5(lap, case["lap"][0], case["lap"][1], V)
         argv += ["-l", str(lap), "-b", str(kw.get("beta_laplace", 2e-2))]
-    out = subprocess.run(argv + files, capture_output=True, text=True, timeout=300)
+    out = subprocess.run(argv + ["--max_cached_solutions", "3"] + files, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
     o = h5ls(out_path)
     nframes = case["frames"].shape[0]
