@@ -186,6 +186,15 @@ int sart_get_config(const sart_engine* e, sart_config* out);
 int sart_solve(sart_engine* e, const double* measurement, double* solution, int32_t has_guess, int32_t* status,
                int32_t* iterations);
 
+/* Several frames that do NOT start from each other's solutions -- the reference's --no_guess loop, source/main.cpp:131-140
+ * with solution_vec.clear() after every frame -- in one call. Such frames are independent right-hand sides of the same
+ * matrix, so the engine solves them two at a time on a single pass over the matrix per iteration (linear solver, one
+ * rank, fused sweep available for the shape; otherwise the frames are solved one after the other, same results).
+ *   measurements [nframes][nrows], solutions [nframes][nvoxel] (host, double); status, iterations [nframes] or NULL.
+ * Every frame gets exactly what sart_solve(has_guess = 0) would give it, within the parity tolerance. */
+int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements, double* solutions, int32_t* status,
+                     int32_t* iterations);
+
 /* The same solve split at the host<->device copies, for callers that keep frames and solutions on the device
  * (time series with warm start: the previous solution never leaves HBM). sart_solve == stage_measurement
  * [+ stage_guess] + solve_resident + fetch_solution. */

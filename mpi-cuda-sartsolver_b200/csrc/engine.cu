@@ -130,6 +130,17 @@ struct sart_engine {
     uint64_t xchg_buf_off[2] = {0, 0};
     unsigned long long xchg_epoch = 0;
     bool peer_exchange = false;
+    // two-frames-per-sweep path (sart_solve_batch): geometry + buffers, allocated on first use
+    bool pair_planned = false, pair_ok = false;
+    uint32_t pr_cluster = 0, pr_wc = 0, pr_stages = 0, pr_stage_bytes = 0, pr_smem = 0, pr_nclusters = 0;
+    void (*pr_kernel)(const sart::FusedArgs) = nullptr;
+    double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr;
+    double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [2][V]
+    float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [2][ld]
+    float *d_pg = nullptr, *d_ppart = nullptr;
+    FrameScalars* d_pfs = nullptr;           // [2]
+    IterState* d_pst[2] = {nullptr, nullptr};  // [parity] -> [2]
+    IterState* h_pst = nullptr;              // pinned, 2 slots x 2 frames
     // pinned staging ring of the file loader (allocated on first use)
     static constexpr int kStagingBuffers = 3;
     char* h_staging[kStagingBuffers] = {nullptr, nullptr, nullptr};
@@ -229,7 +240,14 @@ constexpr int kFusedThreads = 448;  // consumer threads
 template <int K>
 FusedKernel pick_fused_kernel(int k) {
     if constexpr (K > kFusedKMax) return nullptr;
-    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K> : pick_fused_kernel<K + 1>(k);
+    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K, 1> : pick_fused_kernel<K + 1>(k);
+}
+// two frames per sweep: twice the register slices, so at most 4 float4 columns per thread
+constexpr int kFusedKMaxPair = 4;
+template <int K>
+FusedKernel pick_fused_pair_kernel(int k) {
+    if constexpr (K > kFusedKMaxPair) return nullptr;
+    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K, 2> : pick_fused_pair_kernel<K + 1>(k);
 }
 
 // Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
@@ -323,6 +341,7 @@ int launch_fused(sart_engine* e, const float* x, const IterState* st) {
     a.part = e->d_part;
     a.f2part = e->d_f2part;
     a.st = st;
+    a.x_stride = a.g_stride = a.part_stride = a.f2_stride = 0;
     a.Wc = e->fu_wc;
     a.stages = e->fu_stages;
     a.stage_bytes = e->fu_stage_bytes;
@@ -680,6 +699,218 @@ int run_solve(sart_engine* e, int has_guess) {
     return SART_OK;
 }
 
+// ---- two frames per sweep ---------------------------------------------------------------------------------------------
+// Frames solved without a warm start are independent right-hand sides of the same matrix, so two of them can ride on
+// one pass over it (fused_sweep_kernel<.., B = 2>: the row panel is loaded once and read twice from shared memory as
+// before, only the register slices of x and s and the FMAs double). Linear solver, one rank; everything else falls
+// back to solving the frames one after the other.
+int plan_pair(sart_engine* e) {
+    if (e->pair_planned) return SART_OK;
+    e->pair_planned = true;
+    e->pair_ok = false;
+    if (e->cfg.nranks > 1 || e->cfg.logarithmic || e->cfg.sweep_mode == SART_SWEEP_SPLIT) return SART_OK;
+    const uint32_t nt = kFusedThreads, nw = nt / 32;
+    const uint64_t max_wc = (uint64_t)nt * kFusedKMaxPair;
+    uint32_t C = 0;
+    for (uint32_t c : {1u, 2u, 4u, 8u, 16u})
+        if (ceil_div(e->ld4, c) <= max_wc) {
+            C = c;
+            break;
+        }
+    if (!C) return SART_OK;
+    const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
+    const uint32_t stage_bytes = (uint32_t)(ceil_div((uint64_t)wc * 16, 128) * 128);
+    int max_smem = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+    uint32_t S = 0, smem = 0;
+    for (uint32_t st = 8; st >= 2; --st) {
+        const uint64_t need = (uint64_t)st * stage_bytes + (uint64_t)2 * st * 2 * nw * 4 + (uint64_t)2 * st * 2 * 16 * 4 + (uint64_t)6 * st * 8;
+        if (need <= (uint64_t)max_smem) {
+            S = st;
+            smem = (uint32_t)need;
+            break;
+        }
+    }
+    if (!S) return SART_OK;
+    FusedKernel k = pick_fused_pair_kernel<1>((int)ceil_div(wc, nt));
+    if (!k) return SART_OK;
+    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (C > 8) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.gridDim = dim3(C * (uint32_t)e->sm_count, 1, 1);
+    cfg.blockDim = dim3(nt + 64, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int nclusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&nclusters, k, &cfg) != cudaSuccess || nclusters <= 0) {
+        (void)cudaGetLastError();
+        return SART_OK;
+    }
+    e->pr_cluster = C;
+    e->pr_wc = wc;
+    e->pr_stages = S;
+    e->pr_stage_bytes = stage_bytes;
+    e->pr_smem = smem;
+    e->pr_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
+    e->pr_kernel = k;
+
+    SART_TRY(dev_alloc(&e->d_pgd, 2 * e->P));
+    SART_TRY(dev_alloc(&e->d_pg, 2 * e->P));
+    SART_TRY(dev_alloc(&e->d_pxio, 2 * e->V));
+    SART_TRY(dev_alloc(&e->d_psred, 2 * (e->V + 2)));
+    SART_TRY(dev_alloc(&e->d_pf2part, 2 * (uint64_t)e->pr_nclusters));
+    SART_TRY(dev_alloc(&e->d_ppart, 2 * (uint64_t)e->pr_nclusters * e->ld));
+    SART_TRY(dev_alloc(&e->d_pfs, 2));
+    for (int k2 = 0; k2 < 2; ++k2) {
+        SART_TRY(dev_alloc(&e->d_pxd[k2], 2 * e->V));
+        SART_TRY(dev_alloc(&e->d_pxf[k2], 2 * e->ld));
+        SART_TRY(dev_alloc(&e->d_pst[k2], 2));
+    }
+    CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_pst), 4 * sizeof(IterState)));
+    e->pair_ok = true;
+    return SART_OK;
+}
+
+// Two frames from d_pgd[0..1] to d_pxio[0..1] (device resident), default initial guess, linear solver, one rank.
+int run_solve_pair(sart_engine* e, IterState fin[2]) {
+    const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256), pblocks = (uint32_t)ceil_div(e->P, 256);
+    const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
+    const uint64_t P = e->P, V = e->V, ld = e->ld;
+    // per frame: statistics, normalisation, default initial guess (one two-kernel back projection each)
+    for (int b = 0; b < 2; ++b) {
+        frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_pgd + b * P, P, e->d_pfs + b);
+        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + b * P, P, e->d_pfs + b, e->d_lambda,
+                                                             e->cfg.ray_length_threshold, e->d_pg + b * P, e->d_rinv, e->d_w,
+                                                             gpu_sem ? 2 : 1);
+        CUDA_TRY(cudaGetLastError());
+        e->launches += 2;
+        SART_TRY(backproject_weights(e));
+        start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, nullptr, e->d_rho, e->cfg.ray_density_threshold,
+                                                              e->d_pfs + b, gpu_sem ? 1.e-7 : 0.0, 0.0, 0, e->d_pxd[0] + b * V,
+                                                              e->d_pxf[0] + b * ld, V);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+    }
+    init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0], e->d_pst[1]);
+    init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0] + 1, e->d_pst[1] + 1);
+    CUDA_TRY(cudaGetLastError());
+    e->launches += 2;
+    CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
+
+    auto enqueue = [&](int t) -> int {
+        const IterState* st_in = e->d_pst[t & 1];
+        IterState* st_out = e->d_pst[(t + 1) & 1];
+        FusedArgs a;
+        a.H = e->dH;
+        a.ld4 = e->ld4;
+        a.P = P;
+        a.x = e->d_pxf[t & 1];
+        a.g = e->d_pg;
+        a.rinv = e->d_rinv;
+        a.part = e->d_ppart;
+        a.f2part = e->d_pf2part;
+        a.st = st_in;
+        a.x_stride = ld;
+        a.g_stride = P;
+        a.part_stride = (uint64_t)e->pr_nclusters * ld;
+        a.f2_stride = e->pr_nclusters;
+        a.Wc = e->pr_wc;
+        a.stages = e->pr_stages;
+        a.stage_bytes = e->pr_stage_bytes;
+        a.log_mode = 0;
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = e->pr_cluster;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(e->pr_cluster * e->pr_nclusters, 1, 1);
+        cfg.blockDim = dim3(kFusedThreads + 64, 1, 1);
+        cfg.dynamicSmemBytes = e->pr_smem;
+        cfg.stream = e->stream;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        const bool prof = e->profiling && t < kProfiledSweeps;
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+        CUDA_TRY(cudaLaunchKernelEx(&cfg, e->pr_kernel, a));
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        ++e->launches;
+        for (int b = 0; b < 2; ++b) {
+            double* sred = e->d_psred + b * (V + 2);
+            reduce_partials_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_ppart + b * a.part_stride, e->pr_nclusters, ld, V, sred,
+                                                                   st_in + b);
+            SART_TRY(launch_decide(e, t, e->d_pf2part + b * e->pr_nclusters, e->pr_nclusters, st_in + b, st_out + b));
+            UpdArgs u = make_update_args(e, t, st_out + b);
+            u.sred = sred;
+            u.xd_cur = e->d_pxd[t & 1] + b * V;
+            u.xd_next = e->d_pxd[(t + 1) & 1] + b * V;
+            u.xf_next = e->d_pxf[(t + 1) & 1] + b * ld;
+            u.fs = e->d_pfs + b;
+            update_kernel<<<vblocks, 256, 0, e->stream>>>(u);
+            CUDA_TRY(cudaGetLastError());
+            e->launches += 2;
+        }
+        return SART_OK;
+    };
+
+    const int t_max = e->cfg.max_iterations;
+    int t = 0, slot = 0, done_slot = -1;
+    std::deque<int> in_flight;
+    while (true) {
+        if (t <= t_max) {
+            const int nb = std::min(e->batch, t_max - t + 1);
+            for (int i = 0; i < nb; ++i) SART_TRY(enqueue(t + i));
+            t += nb;
+            CUDA_TRY(cudaMemcpyAsync(&e->h_pst[2 * slot], e->d_pst[t & 1], 2 * sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaEventRecord(e->ev_batch[slot], e->stream));
+            in_flight.push_back(slot);
+            slot ^= 1;
+        }
+        if (in_flight.size() == 2 || t > t_max) {
+            if (in_flight.empty()) return fail(SART_ERR_STATE, "pair solve ended without a decision (internal error)");
+            const int sl = in_flight.front();
+            in_flight.pop_front();
+            CUDA_TRY(cudaEventSynchronize(e->ev_batch[sl]));
+            if (e->h_pst[2 * sl].done && e->h_pst[2 * sl + 1].done) {
+                done_slot = sl;
+                break;
+            }
+        }
+    }
+    fin[0] = e->h_pst[2 * done_slot];
+    fin[1] = e->h_pst[2 * done_slot + 1];
+    for (int b = 0; b < 2; ++b) {
+        finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_pxd[0] + b * V, e->d_pxd[1] + b * V, e->d_pst[t & 1] + b,
+                                                               e->d_pfs + b, e->d_pxio + b * V, V);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+    }
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_it0, e->ev_batch[done_slot]));
+    e->stats.iterate_ms = ms;
+    const int its = std::max(fin[0].iterations, fin[1].iterations);
+    e->stats.fused_ms_avg = 0;
+    e->stats.fused_launches = 0;
+    if (e->profiling) {
+        const int n = std::min(kProfiledSweeps, its + 1);
+        double tot = 0;
+        for (int k = 0; k < n; ++k) {
+            float a = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][2], e->ev_prof[k][3]));
+            tot += a;
+        }
+        e->stats.fused_ms_avg = n ? tot / n : 0;
+        e->stats.fused_launches = n;
+    }
+    return SART_OK;
+}
+
 int build_laplacian(sart_engine* e) {
     // with several ranks the reference hands the matrix to rank 0 only (source/main.cpp:73-74): share rank 0's copy
     if (e->cfg.nranks > 1) {
@@ -842,6 +1073,11 @@ void free_engine(sart_engine* e) {
         if (p) cudaIpcCloseMemHandle(p);
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
+    void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
+                         e->d_pg, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
+    for (void* p : pair_ptrs)
+        if (p) cudaFree(p);
+    if (e->h_pst) cudaFreeHost(e->h_pst);
     void* ptrs[] = {e->dH, e->d_rho, e->d_lambda, e->d_lap_rowptr, e->d_lap_col, e->d_lap_val, e->d_gd, e->d_xio,
                     e->d_obs, e->d_sred, e->d_f2part, e->d_f2, e->d_xd[0], e->d_xd[1], e->d_xf[0], e->d_xf[1], e->d_g,
                     e->d_rinv, e->d_fit, e->d_w, e->d_part, e->d_fs, e->d_st[0], e->d_st[1]};
@@ -1280,6 +1516,64 @@ int sart_solve(sart_engine* e, const double* measurement, double* solution, int3
     e->guess_staged = true;
     if (status) *status = e->stats.status;
     if (iterations) *iterations = e->stats.iterations;
+    return SART_OK;
+}
+
+int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements, double* solutions, int32_t* status,
+                     int32_t* iterations) {
+    SART_TRY(require(e, true));
+    if (nframes < 0 || (nframes > 0 && (!measurements || !solutions)))
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_solve_batch: NULL buffers or negative frame count");
+    SART_TRY(plan_pair(e));
+    int32_t f = 0;
+    int total_launches = 0;
+    double total_ms = 0;
+    uint64_t h2d = 0, d2h = 0;
+    while (f < nframes) {
+        if (e->pair_ok && f + 1 < nframes) {
+            e->launches = 0;
+            CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
+            for (int b = 0; b < 2; ++b)
+                CUDA_TRY(cudaMemcpyAsync(e->d_pgd + b * e->P, measurements + (uint64_t)(f + b) * e->P, e->P * sizeof(double),
+                                         cudaMemcpyHostToDevice, e->stream));
+            IterState fin[2];
+            SART_TRY(run_solve_pair(e, fin));
+            for (int b = 0; b < 2; ++b)
+                CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)(f + b) * e->V, e->d_pxio + b * e->V, e->V * sizeof(double),
+                                         cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+            CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+            float ms = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
+            total_ms += ms;
+            total_launches += e->launches;
+            h2d += 2 * e->P * sizeof(double);
+            d2h += 2 * e->V * sizeof(double);
+            for (int b = 0; b < 2; ++b) {
+                if (status) status[f + b] = fin[b].status;
+                if (iterations) iterations[f + b] = fin[b].iterations;
+            }
+            e->stats.status = fin[1].status;
+            e->stats.iterations = fin[1].iterations;
+            e->stats.sweep_mode = SART_SWEEP_FUSED;
+            f += 2;
+        } else {
+            int32_t st = 0, it = 0;
+            SART_TRY(sart_solve(e, measurements + (uint64_t)f * e->P, solutions + (uint64_t)f * e->V, 0, &st, &it));
+            if (status) status[f] = st;
+            if (iterations) iterations[f] = it;
+            total_ms += e->stats.solve_ms;
+            total_launches += e->stats.gpu_launches;
+            h2d += e->stats.h2d_bytes;
+            d2h += e->stats.d2h_bytes;
+            f += 1;
+        }
+    }
+    e->stats.solve_ms = total_ms;
+    e->stats.gpu_launches = total_launches;
+    e->stats.h2d_bytes = h2d;
+    e->stats.d2h_bytes = d2h;
+    e->guess_staged = false;
     return SART_OK;
 }
 

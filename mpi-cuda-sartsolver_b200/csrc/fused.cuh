@@ -114,12 +114,13 @@ struct FusedArgs {
     const float* H;        // [P][ld]
     uint64_t ld4;          // ld / 4
     uint64_t P;
-    const float* x;        // [ld]
-    const float* g;        // [P] normalised measurement
-    const float* rinv;     // [P]
-    float* part;           // [nclusters][ld] per-cluster partial back projection
-    double* f2part;        // [nclusters] per-cluster sum(fit^2)
-    const IterState* st;   // may be null
+    const float* x;        // [B][x_stride] solution(s), zero beyond nvoxel
+    const float* g;        // [B][g_stride] normalised measurement(s)
+    const float* rinv;     // [P] (shared by the frames: it depends on the matrix only)
+    float* part;           // [B][part_stride] = per frame [nclusters][ld] per-cluster partial back projection
+    double* f2part;        // [B][f2_stride]   = per frame [nclusters] per-cluster sum(fit^2)
+    const IterState* st;   // [B] or null
+    uint64_t x_stride, g_stride, part_stride, f2_stride;  // element strides between frames (unused when B == 1)
     uint32_t Wc;           // float4 columns per CTA panel (last panel may be narrower)
     uint32_t stages;       // S >= 2
     uint32_t stage_bytes;  // bytes of one stage, multiple of 128
@@ -139,11 +140,19 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
 
 // warps 0..NWC-1 consumers, warp NWC TMA producer, warp NWC+1 reducer: 16 warps in all, so that every SM sub-partition
 // holds 4 and a thread may use 128 registers (a 17th warp caps the kernel at 96 and spills).
-// shared memory: [S stages][2S x NWC warp partials][2S x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
+// B = frames solved by the same sweep (independent right-hand sides that share the matrix: time series without warm
+// start). The matrix row is loaded once and read twice from shared memory whatever B is; only the FMAs, the register
+// slices of x and s, and the exchanged scalars are per frame.
+// shared memory: [S stages][2S x B x NWC warp partials][2S x B x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
 // All ring / slot / barrier positions advance incrementally (no integer division in the row loop).
-template <int NT, int K>
+template <int NT, int K, int B>
 __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
-    if (a.st && a.st->done) return;
+    if (a.st) {
+        bool all_done = true;
+#pragma unroll
+        for (int b = 0; b < B; ++b) all_done = all_done && a.st[b].done;
+        if (all_done) return;
+    }
     constexpr uint32_t NWC = NT / 32;
     constexpr uint32_t CSTRIDE = 16;  // floats per slot of per-CTA sums (cluster size <= 16), 64-byte aligned
     extern __shared__ __align__(128) unsigned char smem[];
@@ -153,9 +162,9 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     const uint32_t ring_u32 = smem_u32(smem);
-    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][NWC] floats
-    const uint32_t cdot_u32 = wpart_u32 + 2 * S * NWC * 4;           // [2S][CSTRIDE] floats
-    const uint32_t full_u32 = cdot_u32 + 2 * S * CSTRIDE * 4;
+    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][B][NWC] floats
+    const uint32_t cdot_u32 = wpart_u32 + 2 * S * B * NWC * 4;       // [2S][B][CSTRIDE] floats
+    const uint32_t full_u32 = cdot_u32 + 2 * S * B * CSTRIDE * 4;
     const uint32_t empty_u32 = full_u32 + 8 * S, wbar_u32 = empty_u32 + 8 * S, dot_u32 = wbar_u32 + 16 * S;
 
     if (tid == 0) {
@@ -184,7 +193,7 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             uint32_t stage = 0, slot = 0, empty_parity = 1;
             for (uint32_t t = 0; t < n; ++t) {
                 mbar_wait(empty_u32 + 8 * stage, empty_parity);
-                mbar_expect_tx(dot_u32 + 8 * slot, 4 * C);  // one float from every CTA of the cluster
+                mbar_expect_tx(dot_u32 + 8 * slot, 4 * C * B);  // one float per frame from every CTA of the cluster
                 mbar_expect_tx(full_u32 + 8 * stage, bytes);
                 bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
                 src += src_step;
@@ -197,16 +206,19 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
         }
         __syncwarp();
     } else if (warp == NWC + 1) {
-        // ---- reducer: CTA-level sum of the warp partials, one message per peer -----------------------------------------
+        // ---- reducer: CTA-level sum of the warp partials, one message per peer (and frame) -------------------------------
         const uint32_t peer = (lane < C) ? lane : 0;
         const uint32_t peer_cdot0 = map_to_cta(cdot_u32 + rank * 4, peer);
         const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
         uint32_t slot = 0, parity = 0;
         for (uint32_t t = 0; t < n; ++t) {
             mbar_wait(wbar_u32 + 8 * slot, parity);
-            float p = (lane < NWC) ? lds32(wpart_u32 + (slot * NWC + lane) * 4) : 0.f;
-            p = warp_sum_f32(p);  // fixed tree over the NWC partials
-            if (lane < C) st_async_remote_f32(peer_cdot0 + slot * (CSTRIDE * 4), p, peer_dot0 + 8 * slot);
+#pragma unroll
+            for (int b = 0; b < B; ++b) {
+                float p = (lane < NWC) ? lds32(wpart_u32 + ((slot * B + b) * NWC + lane) * 4) : 0.f;
+                p = warp_sum_f32(p);  // fixed tree over the NWC partials
+                if (lane < C) st_async_remote_f32(peer_cdot0 + (slot * B + b) * (CSTRIDE * 4), p, peer_dot0 + 8 * slot);
+            }
             if (++slot == 2 * S) {
                 slot = 0;
                 parity ^= 1;
@@ -216,44 +228,57 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     } else {
         // ---- consumers -----------------------------------------------------------------------------------------------
         const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
-        float4 xr[K], sacc[K];
-        {
-            const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x) + c0 + tid;
+        float4 xr[B][K], sacc[B][K];
+#pragma unroll
+        for (int b = 0; b < B; ++b) {
+            const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x + b * a.x_stride) + c0 + tid;
 #pragma unroll
             for (int m = 0; m < K; ++m) {
-                xr[m] = (m < mine) ? __ldg(x4 + m * NT) : make_float4(0.f, 0.f, 0.f, 0.f);
-                sacc[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+                xr[b][m] = (m < mine) ? __ldg(x4 + m * NT) : make_float4(0.f, 0.f, 0.f, 0.f);
+                sacc[b][m] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
         }
-        double f2acc = 0.0;
+        double f2acc[B];
+#pragma unroll
+        for (int b = 0; b < B; ++b) f2acc[b] = 0.0;
         uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0;
         uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
         const float* gp = a.g + cid;
         const float* rp = a.rinv + cid;
-        float g_cur = 0.f, r_cur = 0.f, g_nxt = 0.f, r_nxt = 0.f;
+        float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
         const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
 
-        auto forward = [&](float& g_out, float& r_out) {
-            g_out = __ldg(gp);
+        auto forward = [&](float (&g_out)[B], float& r_out) {
+#pragma unroll
+            for (int b = 0; b < B; ++b) g_out[b] = __ldg(gp + b * a.g_stride);  // consumed one pipeline step later
             r_out = __ldg(rp);
             gp += ncl;
             rp += ncl;
             mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
             const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            float acc[B][4];
+#pragma unroll
+            for (int b = 0; b < B; ++b) acc[b][0] = acc[b][1] = acc[b][2] = acc[b][3] = 0.f;
 #pragma unroll
             for (int m = 0; m < K; ++m)
                 if (m < mine) {
                     const float4 h = lds128(base + m * (NT * 16));
-                    a0 = fmaf(h.x, xr[m].x, a0);
-                    a1 = fmaf(h.y, xr[m].y, a1);
-                    a2 = fmaf(h.z, xr[m].z, a2);
-                    a3 = fmaf(h.w, xr[m].w, a3);
+#pragma unroll
+                    for (int b = 0; b < B; ++b) {
+                        acc[b][0] = fmaf(h.x, xr[b][m].x, acc[b][0]);
+                        acc[b][1] = fmaf(h.y, xr[b][m].y, acc[b][1]);
+                        acc[b][2] = fmaf(h.z, xr[b][m].z, acc[b][2]);
+                        acc[b][3] = fmaf(h.w, xr[b][m].w, acc[b][3]);
+                    }
                 }
-            const float acc = warp_sum_f32((a0 + a1) + (a2 + a3));
+            float tot[B];
+#pragma unroll
+            for (int b = 0; b < B; ++b) tot[b] = warp_sum_f32((acc[b][0] + acc[b][1]) + (acc[b][2] + acc[b][3]));
             if (lane == 0) {
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + (fp_slot * NWC + warp) * 4), "f"(acc) : "memory");
-                mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partial
+#pragma unroll
+                for (int b = 0; b < B; ++b)
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + ((fp_slot * B + b) * NWC + warp) * 4), "f"(tot[b]) : "memory");
+                mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partials
             }
             if (++fp_stage == S) {
                 fp_stage = 0;
@@ -262,30 +287,37 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             if (++fp_slot == 2 * S) fp_slot = 0;
         };
 
-        auto finish = [&](float gi, float ri) {
+        auto finish = [&](const float (&gi)[B], float ri) {
             mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
-            // the C per-CTA sums in rank order: the same additions in every thread of the cluster
-            float fitv = 0.f;
-            const uint32_t cd = cdot_u32 + fin_slot * (CSTRIDE * 4);
-            for (uint32_t q = 0; q < c4; ++q) {
-                const float4 v = lds128(cd + q * 16);
-                fitv += v.x;
-                if (4 * q + 1 < C) fitv += v.y;
-                if (4 * q + 2 < C) fitv += v.z;
-                if (4 * q + 3 < C) fitv += v.w;
+            float wi[B];
+#pragma unroll
+            for (int b = 0; b < B; ++b) {
+                // the C per-CTA sums in rank order: the same additions in every thread of the cluster
+                float fitv = 0.f;
+                const uint32_t cd = cdot_u32 + (fin_slot * B + b) * (CSTRIDE * 4);
+                for (uint32_t q = 0; q < c4; ++q) {
+                    const float4 v = lds128(cd + q * 16);
+                    fitv += v.x;
+                    if (4 * q + 1 < C) fitv += v.y;
+                    if (4 * q + 2 < C) fitv += v.z;
+                    if (4 * q + 3 < C) fitv += v.w;
+                }
+                wi[b] = 0.f;
+                if (gi[b] >= 0.f) wi[b] = a.log_mode ? fitv * ri : (gi[b] - fitv) * ri;
+                f2acc[b] += (double)fitv * (double)fitv;
             }
-            float wi = 0.f;
-            if (gi >= 0.f) wi = a.log_mode ? fitv * ri : (gi - fitv) * ri;
-            f2acc += (double)fitv * (double)fitv;
             const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
 #pragma unroll
             for (int m = 0; m < K; ++m)
                 if (m < mine) {
                     const float4 h = lds128(base + m * (NT * 16));
-                    sacc[m].x = fmaf(h.x, wi, sacc[m].x);
-                    sacc[m].y = fmaf(h.y, wi, sacc[m].y);
-                    sacc[m].z = fmaf(h.z, wi, sacc[m].z);
-                    sacc[m].w = fmaf(h.w, wi, sacc[m].w);
+#pragma unroll
+                    for (int b = 0; b < B; ++b) {
+                        sacc[b][m].x = fmaf(h.x, wi[b], sacc[b][m].x);
+                        sacc[b][m].y = fmaf(h.y, wi[b], sacc[b][m].y);
+                        sacc[b][m].z = fmaf(h.z, wi[b], sacc[b][m].z);
+                        sacc[b][m].w = fmaf(h.w, wi[b], sacc[b][m].w);
+                    }
                 }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_u32 + 8 * fin_stage);
@@ -301,17 +333,21 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             for (uint32_t t = 0; t + 1 < n; ++t) {
                 forward(g_nxt, r_nxt);
                 finish(g_cur, r_cur);
-                g_cur = g_nxt;
+#pragma unroll
+                for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
                 r_cur = r_nxt;
             }
             finish(g_cur, r_cur);
         }
 
-        float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part) + (uint64_t)cid * a.ld4 + c0 + tid;
 #pragma unroll
-        for (int m = 0; m < K; ++m)
-            if (m < mine) out4[m * NT] = sacc[m];
-        if (rank == 0 && tid == 0) a.f2part[cid] = f2acc;
+        for (int b = 0; b < B; ++b) {
+            float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part + b * a.part_stride) + (uint64_t)cid * a.ld4 + c0 + tid;
+#pragma unroll
+            for (int m = 0; m < K; ++m)
+                if (m < mine) out4[m * NT] = sacc[b][m];
+            if (rank == 0 && tid == 0) a.f2part[b * a.f2_stride + cid] = f2acc[b];
+        }
     }
     cluster_sync_all();
 }

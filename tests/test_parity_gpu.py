@@ -449,3 +449,35 @@ def test_randomised_problems_against_the_oracle(seed, sart, restatement):
         assert rel_l2(x, x_ref) <= TOL, dict(P=P, V=V, mode=mode, gpu_sem=gpu_sem, **kw)
     else:
         np.testing.assert_array_equal(np.isfinite(x), np.isfinite(x_ref))
+
+
+@pytest.mark.parametrize("P,V,tol", [(700, 1000, None), (512, 50000, None), (300, 20000, 1e-4), (257, 77, 1e-4)])
+def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, sart, restatement):
+    """sart_solve_batch (two frames per matrix sweep) against solving every frame on its own and against the oracle: five
+    frames, so two pairs and one single; frames of one pair converge at different iterations when the tolerance decides."""
+    syn = load_synthetic()
+    H = restatement.fill_synthetic(P, V, 321)
+    frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=t) * (1.0 + 3.0 * t)) for t in (0.0, 0.3, 0.55, 0.8, 1.0)])
+    frames[1, ::19] = -1.0
+    lap = syn.laplacian_coo(V)
+    kw = dict(beta_laplace=2e-2, max_iterations=9, fixed_iterations=True) if tol is None else \
+        dict(beta_laplace=2e-2, max_iterations=300, conv_tolerance=tol)
+    with sart.Engine(P, V, device=0, **kw) as eng:
+        eng.upload_rows(H)
+        eng.set_laplacian(*lap)
+        eng.finalize()
+        xb, stb, itb = eng.solve_batch(frames)
+        singles = [eng.solve(f) for f in frames]
+    for f in range(5):
+        xs, sts, its = singles[f]
+        assert abs(int(itb[f]) - its) <= 1
+        if itb[f] == its:
+            assert stb[f] == sts and rel_l2(xb[f], xs) <= 1e-6
+        okw = dict(kw)
+        okw.pop("fixed_iterations", None)
+        x_ref, st_ref, it_ref = restatement.solve(H, frames[f], lap=lap, fixed_iterations=tol is None, **okw)
+        assert abs(int(itb[f]) - it_ref) <= 1
+        if itb[f] == it_ref:
+            assert stb[f] == st_ref and rel_l2(xb[f], x_ref) <= TOL
+    if tol is not None:
+        assert len(set(itb.tolist())) > 1  # the frames really stopped at different iterations
