@@ -236,22 +236,13 @@ int main(int argc, char* argv[]) {
     std::vector<std::vector<double>> all_camera_time;
     std::vector<int32_t> all_status, all_iterations;
 
-    // source/main.cpp:127-140
-    std::vector<double> solution_vec, frame;
-    for (size_t k = 0; k < frames->size(); ++k) {
-        if (!frames->read(k, offset_pixel, npixel_local, frame, error)) die(error);
-        const auto last = std::chrono::steady_clock::now();
-        const int has_guess = solution_vec.empty() ? 0 : 1;
-        if (!has_guess) solution_vec.resize(nvoxel);
-        int32_t status = 0, iterations = 0;
-        must(sart_solve(engine, frame.data(), solution_vec.data(), has_guess, &status, &iterations));
-        const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
-        if (rank == 0) std::cout << "Processed in: " << duration.count() << " ms" << std::endl;
+    // source/main.cpp:127-140. With --no_guess consecutive frames do not depend on each other, so they are handed to the
+    // engine two at a time (sart_solve_batch: one pass over the matrix per iteration serves both).
+    auto store = [&](size_t k, const double* x, int32_t status, int32_t iterations) {
         const double t = frames->frame_time(k);
-        if (rank != 0) {
-            // source/main.cpp:134: only the root stores solutions
-        } else if (h5_out) {
-            all_values.insert(all_values.end(), solution_vec.begin(), solution_vec.end());
+        if (rank != 0) return;  // source/main.cpp:134: only the root stores solutions
+        if (h5_out) {
+            all_values.insert(all_values.end(), x, x + nvoxel);
             all_time.push_back(t);
             all_camera_time.push_back(frames->camera_frame_time(k));
             all_status.push_back(status);
@@ -260,19 +251,53 @@ int main(int argc, char* argv[]) {
             std::fwrite(&t, sizeof(double), 1, out);
             std::fwrite(&status, sizeof(int32_t), 1, out);
             std::fwrite(&iterations, sizeof(int32_t), 1, out);
-            std::fwrite(solution_vec.data(), sizeof(double), nvoxel, out);
+            std::fwrite(x, sizeof(double), nvoxel, out);
         }
-        if (config.no_guess) solution_vec.clear();
+    };
+    auto flush = [&](size_t done) {
         // source/solution.cpp:55, 167-180: the reference appends to the file every max_cached_solutions frames so that a
         // long run leaves its results behind if it dies; with a write-once container the file is rewritten instead
-        if (h5_out && rank == 0 && (k + 1) % (size_t)config.max_cached_solutions == 0 && k + 1 < frames->size()) {
-            try {
-                h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time,
-                                         all_status, all_iterations, h5.grid);
-            } catch (const std::exception& err) {
-                die(err.what());
-            }
+        if (!(h5_out && rank == 0) || done >= frames->size() || done % (size_t)config.max_cached_solutions != 0) return;
+        try {
+            h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time, all_status,
+                                     all_iterations, h5.grid);
+        } catch (const std::exception& err) {
+            die(err.what());
         }
+    };
+    std::vector<double> solution_vec, frame;
+    size_t k = 0;
+    while (k < frames->size()) {
+        const size_t nb = (config.no_guess && k + 1 < frames->size()) ? 2 : 1;
+        if (nb == 2) {
+            std::vector<double> pair_frames(2 * npixel_local), pair_solutions(2 * nvoxel), one;
+            for (size_t b = 0; b < 2; ++b) {
+                if (!frames->read(k + b, offset_pixel, npixel_local, one, error)) die(error);
+                std::copy(one.begin(), one.end(), pair_frames.begin() + b * npixel_local);
+            }
+            const auto last = std::chrono::steady_clock::now();
+            int32_t status[2] = {0, 0}, iterations[2] = {0, 0};
+            must(sart_solve_batch(engine, 2, pair_frames.data(), pair_solutions.data(), status, iterations));
+            const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
+            for (size_t b = 0; b < 2; ++b) {
+                if (rank == 0) std::cout << "Processed in: " << duration.count() / 2 << " ms" << std::endl;
+                store(k + b, pair_solutions.data() + b * nvoxel, status[b], iterations[b]);
+                flush(k + b + 1);
+            }
+        } else {
+            if (!frames->read(k, offset_pixel, npixel_local, frame, error)) die(error);
+            const auto last = std::chrono::steady_clock::now();
+            const int has_guess = solution_vec.empty() ? 0 : 1;
+            if (!has_guess) solution_vec.resize(nvoxel);
+            int32_t status = 0, iterations = 0;
+            must(sart_solve(engine, frame.data(), solution_vec.data(), has_guess, &status, &iterations));
+            const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
+            if (rank == 0) std::cout << "Processed in: " << duration.count() << " ms" << std::endl;
+            store(k, solution_vec.data(), status, iterations);
+            if (config.no_guess) solution_vec.clear();
+            flush(k + 1);
+        }
+        k += nb;
     }
     if (h5_out && rank == 0) {
         try {
