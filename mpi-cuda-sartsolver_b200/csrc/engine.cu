@@ -470,11 +470,12 @@ int launch_xchg_update(sart_engine* e, int t, const IterState* st_in, IterState*
     return SART_OK;
 }
 
-int launch_decide(sart_engine* e, int t, const double* f2, uint32_t n, const IterState* st_in, IterState* st_out) {
+int launch_decide(sart_engine* e, int t, const double* f2, uint32_t n, const IterState* st_in, IterState* st_out,
+                  const FrameScalars* fs = nullptr) {
     DecideArgs d;
     d.f2part = f2;
     d.n = n;
-    d.fs = e->d_fs;
+    d.fs = fs ? fs : e->d_fs;
     d.st_in = st_in;
     d.st_out = st_out;
     d.tol = e->cfg.conv_tolerance;
@@ -845,7 +846,7 @@ int run_solve_pair(sart_engine* e, IterState fin[2]) {
             double* sred = e->d_psred + b * (V + 2);
             reduce_partials_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_ppart + b * a.part_stride, e->pr_nclusters, ld, V, sred,
                                                                    st_in + b);
-            SART_TRY(launch_decide(e, t, e->d_pf2part + b * e->pr_nclusters, e->pr_nclusters, st_in + b, st_out + b));
+            SART_TRY(launch_decide(e, t, e->d_pf2part + b * e->pr_nclusters, e->pr_nclusters, st_in + b, st_out + b, e->d_pfs + b));
             UpdArgs u = make_update_args(e, t, st_out + b);
             u.sred = sred;
             u.xd_cur = e->d_pxd[t & 1] + b * V;
