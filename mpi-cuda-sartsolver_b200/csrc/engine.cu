@@ -237,17 +237,24 @@ typedef void (*FusedKernel)(const FusedArgs);
 // slices of x and s live in registers): the smallest K that covers the panel is instantiated.
 constexpr int kFusedKMax = 8;
 constexpr int kFusedThreads = 448;  // consumer threads
+// pipeline depth: 3 rows ahead when the ring holds 8 stages (short rows), else 1 (long rows, HBM-bound anyway)
+inline int fused_depth(uint32_t stages) {
+    const int want = env_int("SART_FUSED_DEPTH", stages >= 8 ? 3 : 1);
+    return (want >= 3 && stages >= 4) ? 3 : 1;  // the ring must hold the rows in flight plus one being loaded
+}
 template <int K>
-FusedKernel pick_fused_kernel(int k) {
+FusedKernel pick_fused_kernel(int k, int depth) {
     if constexpr (K > kFusedKMax) return nullptr;
-    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K, 1> : pick_fused_kernel<K + 1>(k);
+    else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 1, 3> : fused_sweep_kernel<kFusedThreads, K, 1, 1>;
+    else return pick_fused_kernel<K + 1>(k, depth);
 }
 // two frames per sweep: twice the register slices, so at most 4 float4 columns per thread
 constexpr int kFusedKMaxPair = 4;
 template <int K>
-FusedKernel pick_fused_pair_kernel(int k) {
+FusedKernel pick_fused_pair_kernel(int k, int depth) {
     if constexpr (K > kFusedKMaxPair) return nullptr;
-    else return (k <= K) ? fused_sweep_kernel<kFusedThreads, K, 2> : pick_fused_pair_kernel<K + 1>(k);
+    else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 2, 3> : fused_sweep_kernel<kFusedThreads, K, 2, 1>;
+    else return pick_fused_pair_kernel<K + 1>(k, depth);
 }
 
 // Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
@@ -294,7 +301,7 @@ int plan_fused(sart_engine* e) {
     if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 1024)) return SART_OK;
 
     const int k_need = (int)ceil_div(wc, nt);
-    const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need);
+    const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need, fused_depth(S));
     if (!kFusedKernel) return unavailable("no kernel instance for this panel width");
     e->fu_kernel = kFusedKernel;
     e->fu_threads = nt + 32 * extra_warps;
@@ -733,7 +740,7 @@ int plan_pair(sart_engine* e) {
         }
     }
     if (!S) return SART_OK;
-    FusedKernel k = pick_fused_pair_kernel<1>((int)ceil_div(wc, nt));
+    FusedKernel k = pick_fused_pair_kernel<1>((int)ceil_div(wc, nt), fused_depth(S));
     if (!k) return SART_OK;
     CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (C > 8) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));

@@ -23,10 +23,10 @@
 //       an earlier version let every warp send to every CTA (C x NW messages per row and CTA), which cost 2 % at C = 4
 //       and 20 % at C = 16. No fence anywhere: a plain remote store + mbarrier.arrive.release.cluster is a
 //       MEMBAR.ALL.GPU per row per warp and made the first version 2x slower than two separate sweeps.
-// No __syncthreads in the loop: warps only meet at mbarriers. Slot reuse: a CTA reaches FP(t) only after its own
-// FIN(t-S), which needed every peer's row t-S, which those peers produced after their FIN(t-S-2); with 2S slots (S >= 2)
-// nothing for row t can land before every CTA has consumed row t-2S, and the producer re-arms a slot when it re-issues
-// the stage. At the end each CTA writes its slice of the cluster's partial s; the clusters' partials are added in
+// No __syncthreads in the loop: warps only meet at mbarriers. Slot reuse (pipeline depth D): a CTA reaches FP(t) only
+// after its own FIN(t-S), which needed every peer's row t-S, which those peers produced after their FIN(t-S-D-1); with
+// 2S slots and S >= D+1 nothing for row t can land before every CTA has consumed row t-2S, and the producer re-arms a
+// slot when it re-issues the stage. At the end each CTA writes its slice of the cluster's partial s; the clusters' partials are added in
 // fixed order by reduce_partials_kernel, exactly like the slabs of the two-kernel path. Replaces cublasSgemv +
 // cublasSdot + PropagateKernel's prologue and main loop (source/sartsolver_cuda.cpp:239-253,
 // source/cuda/sart_kernels.cu:63-101) in one launch.
@@ -143,9 +143,12 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
 // B = frames solved by the same sweep (independent right-hand sides that share the matrix: time series without warm
 // start). The matrix row is loaded once and read twice from shared memory whatever B is; only the FMAs, the register
 // slices of x and s, and the exchanged scalars are per frame.
+// D = software-pipeline depth of the consumers: FP runs D rows ahead of FIN, so the exchange latency of a row (reducer
+// wake-up, DSMEM hop, barrier) is spread over D rows of work. Long rows (50 KB per CTA: 4 stages fit) are HBM-bound
+// with D = 1; short rows (8 stages fit) need D = 3. Requires S >= D + 1 (ring) and 2S >= S + D + 1 (slot reuse, below).
 // shared memory: [S stages][2S x B x NWC warp partials][2S x B x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
 // All ring / slot / barrier positions advance incrementally (no integer division in the row loop).
-template <int NT, int K, int B>
+template <int NT, int K, int B, int D>
 __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
     if (a.st) {
         bool all_done = true;
@@ -245,7 +248,14 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
         uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
         const float* gp = a.g + cid;
         const float* rp = a.rinv + cid;
-        float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
+        // measurements / inverse ray lengths of the rows in flight: [0] = the row FIN handles next, [D] = newest
+        float g_q[D + 1][B], r_q[D + 1];
+#pragma unroll
+        for (int d = 0; d <= D; ++d) {
+            r_q[d] = 0.f;
+#pragma unroll
+            for (int b = 0; b < B; ++b) g_q[d][b] = 0.f;
+        }
         const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
 
         auto forward = [&](float (&g_out)[B], float& r_out) {
@@ -328,16 +338,19 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             }
         };
 
-        if (n > 0) {
-            forward(g_cur, r_cur);
-            for (uint32_t t = 0; t + 1 < n; ++t) {
-                forward(g_nxt, r_nxt);
-                finish(g_cur, r_cur);
+        // prologue: the first D rows go through FP; then FP(t + D) ; FIN(t) ; shift the queue
 #pragma unroll
-                for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
-                r_cur = r_nxt;
+        for (int d = 0; d < D; ++d)
+            if ((uint32_t)d < n) forward(g_q[d], r_q[d]);
+        for (uint32_t t = 0; t < n; ++t) {
+            if (t + D < n) forward(g_q[D], r_q[D]);
+            finish(g_q[0], r_q[0]);
+#pragma unroll
+            for (int d = 0; d < D; ++d) {
+                r_q[d] = r_q[d + 1];
+#pragma unroll
+                for (int b = 0; b < B; ++b) g_q[d][b] = g_q[d + 1][b];
             }
-            finish(g_cur, r_cur);
         }
 
 #pragma unroll

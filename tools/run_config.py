@@ -40,6 +40,9 @@ def main():
     ap.add_argument("--iterations", type=int, default=5)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the row count (debugging on fewer GPUs)")
     ap.add_argument("--sweep", default="auto", choices=["auto", "split", "fused"])
+    ap.add_argument("--batch", type=int, default=0,
+                    help="c2: solve this many independent frames (no warm start, --iterations each) with sart_solve_batch "
+                         "and one by one, and report both rates")
     args = ap.parse_args()
 
     sart = load_package()
@@ -52,6 +55,7 @@ def main():
     mode = {"auto": 0, "split": 1, "fused": 2}[args.sweep]
 
     t0 = time.perf_counter()
+    series = series and not args.batch
     eng = sart.Engine(P, V, rank=cp.rank, nranks=cp.world, device=device, beta_laplace=2e-2, sweep_mode=mode,
                       max_iterations=2000 if series else args.iterations, fixed_iterations=not series)
     if cp.world > 1:
@@ -66,7 +70,25 @@ def main():
            "shard_gb": eng.nrows * V * 4 / 1e9, "matrix_gb": P * V * 4 / 1e9, "setup_s": t_setup,
            "ray_length_mean": float(lam.mean()), "ray_density_min": float(rho.min())}
 
-    if not series:
+    if args.batch:
+        F = args.batch
+        frames = np.stack([eng.forward_project(syn.emission_profile(V, t=f / max(1, F - 1))) for f in range(F)])
+        eng.solve_batch(frames[:2])  # warm-up (allocates the pair buffers)
+        t1 = time.perf_counter()
+        xb, stb, itb = eng.solve_batch(frames)
+        t_batch = time.perf_counter() - t1
+        pair_ms = eng.stats().fused_ms_avg
+        t1 = time.perf_counter()
+        singles = [eng.solve(f) for f in frames]
+        t_single = time.perf_counter() - t1
+        single_ms = eng.stats().fused_ms_avg
+        worst = max(rel(xb[f], singles[f][0]) for f in range(F))
+        out.update({"batch_frames": F, "iterations_per_frame": int(itb[0]), "batch_s": t_batch, "one_by_one_s": t_single,
+                    "frame_iterations_per_s_batch": float(np.sum(itb)) / t_batch,
+                    "frame_iterations_per_s_one_by_one": float(sum(s[2] for s in singles)) / t_single,
+                    "speedup": t_single / t_batch, "pair_sweep_ms": pair_ms, "single_sweep_ms": single_ms,
+                    "max_rel_l2_batch_vs_single": worst, "x_checksum": float(np.dot(xb[-1], np.arange(1, V + 1)))})
+    elif not series:
         xs = syn.emission_profile(V)
         g = eng.forward_project(xs)
         x1, st, it = eng.solve(g)
