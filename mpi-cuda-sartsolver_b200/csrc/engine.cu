@@ -280,7 +280,9 @@ int plan_fused(sart_engine* e) {
     };
     if (!C) return unavailable("nvoxel exceeds what 16 CTAs can hold in registers");
     const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
-    const uint32_t stage_bytes = (uint32_t)(ceil_div((uint64_t)wc * 16, 128) * 128);
+    const int k_need = (int)ceil_div(wc, nt);
+    // a stage holds K x NT float4 per row panel: the kernel reads all of it and zero-fills what the copy leaves out
+    const uint32_t stage_bytes = (uint32_t)k_need * nt * 16;
     const uint32_t nw = nt / 32;
     const uint32_t extra_warps = 2;  // producer + reducer
     int max_smem = 0;
@@ -300,7 +302,6 @@ int plan_fused(sart_engine* e) {
     // long rows only, unless forced: short rows make the per-row exchange dominate
     if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 1024)) return SART_OK;
 
-    const int k_need = (int)ceil_div(wc, nt);
     const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need, fused_depth(S));
     if (!kFusedKernel) return unavailable("no kernel instance for this panel width");
     e->fu_kernel = kFusedKernel;
@@ -727,7 +728,7 @@ int plan_pair(sart_engine* e) {
         }
     if (!C) return SART_OK;
     const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
-    const uint32_t stage_bytes = (uint32_t)(ceil_div((uint64_t)wc * 16, 128) * 128);
+    const uint32_t stage_bytes = (uint32_t)ceil_div(wc, nt) * nt * 16;
     int max_smem = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
     uint32_t S = 0, smem = 0;

@@ -158,6 +158,8 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     }
     constexpr uint32_t NWC = NT / 32;
     constexpr uint32_t CSTRIDE = 16;  // floats per slot of per-CTA sums (cluster size <= 16), 64-byte aligned
+    // 128-bit shared loads issued back to back before their FMAs (their latency overlaps); bounded by the register budget
+    constexpr int G = (B * K >= 7) ? ((B * K >= 13 || B == 1) ? 1 : 2) : (K < 4 ? K : 4);
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t S = a.stages;
     const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
@@ -170,6 +172,15 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     const uint32_t full_u32 = cdot_u32 + 2 * S * B * CSTRIDE * 4;
     const uint32_t empty_u32 = full_u32 + 8 * S, wbar_u32 = empty_u32 + 8 * S, dot_u32 = wbar_u32 + 16 * S;
 
+    const uint32_t c0 = rank * a.Wc;
+    const uint32_t wcols = ((uint64_t)c0 < a.ld4) ? (uint32_t)min((uint64_t)a.Wc, a.ld4 - c0) : 0u;
+    // What the bulk copies and the peers never write must read as zero, so that the row loop needs no column guards:
+    // the tail of every stage behind the panel (stage_bytes = K * NT float4) and the per-CTA sum slots of ranks >= C.
+    for (uint32_t s = 0; s < S; ++s)
+        for (uint32_t o = (wcols + tid) * 16; o < a.stage_bytes; o += blockDim.x * 16)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %1, %1, %1};" ::"r"(ring_u32 + s * a.stage_bytes + o), "f"(0.f) : "memory");
+    for (uint32_t i = tid; i < 2 * S * B * CSTRIDE; i += blockDim.x)
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(cdot_u32 + 4 * i), "f"(0.f) : "memory");
     if (tid == 0) {
         for (uint32_t s = 0; s < S; ++s) {
             mbar_init(full_u32 + 8 * s, 1);
@@ -184,9 +195,6 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     cluster_sync_all();
 
     const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;
-    const uint32_t c0 = rank * a.Wc;
-    const uint32_t wcols = (uint32_t)min((uint64_t)a.Wc, a.ld4 - c0);
-
     if (warp == NWC) {
         // ---- producer ------------------------------------------------------------------------------------------------
         if (lane == 0) {
@@ -198,7 +206,7 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
                 mbar_wait(empty_u32 + 8 * stage, empty_parity);
                 mbar_expect_tx(dot_u32 + 8 * slot, 4 * C * B);  // one float per frame from every CTA of the cluster
                 mbar_expect_tx(full_u32 + 8 * stage, bytes);
-                bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
+                if (bytes) bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
                 src += src_step;
                 if (++stage == S) {
                     stage = 0;
@@ -246,41 +254,45 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
         for (int b = 0; b < B; ++b) f2acc[b] = 0.0;
         uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0;
         uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
-        const float* gp = a.g + cid;
-        const float* rp = a.rinv + cid;
-        // measurements / inverse ray lengths of the rows in flight: [0] = the row FIN handles next, [D] = newest
-        float g_q[D + 1][B], r_q[D + 1];
+        // Measurements and inverse ray lengths of the cluster's rows are fetched 32 rows at a time: lane l holds row
+        // 32j + l of batch j, the batch after the current one is already in flight, and each row's values are
+        // broadcast with a shuffle. A per-row load, however early it is issued, ends up waited for within the row
+        // (its register is touched when the pipeline queue shifts), which put one exposed L2/HBM latency on every
+        // row and capped short rows at ~0.75 us each.
+        float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
+        auto load_batch = [&](uint32_t t0) {
+            const uint32_t row = t0 + lane;
+            const uint64_t off = (uint64_t)cid + (uint64_t)row * ncl;
 #pragma unroll
-        for (int d = 0; d <= D; ++d) {
-            r_q[d] = 0.f;
-#pragma unroll
-            for (int b = 0; b < B; ++b) g_q[d][b] = 0.f;
-        }
+            for (int b = 0; b < B; ++b) g_nxt[b] = (row < n) ? __ldg(a.g + b * a.g_stride + off) : 0.f;
+            r_nxt = (row < n) ? __ldg(a.rinv + off) : 0.f;
+        };
         const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
 
-        auto forward = [&](float (&g_out)[B], float& r_out) {
-#pragma unroll
-            for (int b = 0; b < B; ++b) g_out[b] = __ldg(gp + b * a.g_stride);  // consumed one pipeline step later
-            r_out = __ldg(rp);
-            gp += ncl;
-            rp += ncl;
+        auto forward = [&]() {
             mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
             const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
             float acc[B][4];
 #pragma unroll
             for (int b = 0; b < B; ++b) acc[b][0] = acc[b][1] = acc[b][2] = acc[b][3] = 0.f;
 #pragma unroll
-            for (int m = 0; m < K; ++m)
-                if (m < mine) {
-                    const float4 h = lds128(base + m * (NT * 16));
+            for (int m0 = 0; m0 < K; m0 += G) {
+                float4 h[G];
 #pragma unroll
-                    for (int b = 0; b < B; ++b) {
-                        acc[b][0] = fmaf(h.x, xr[b][m].x, acc[b][0]);
-                        acc[b][1] = fmaf(h.y, xr[b][m].y, acc[b][1]);
-                        acc[b][2] = fmaf(h.z, xr[b][m].z, acc[b][2]);
-                        acc[b][3] = fmaf(h.w, xr[b][m].w, acc[b][3]);
+                for (int j = 0; j < G; ++j)
+                    if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+                    if (m0 + j < K) {
+#pragma unroll
+                        for (int b = 0; b < B; ++b) {
+                            acc[b][0] = fmaf(h[j].x, xr[b][m0 + j].x, acc[b][0]);
+                            acc[b][1] = fmaf(h[j].y, xr[b][m0 + j].y, acc[b][1]);
+                            acc[b][2] = fmaf(h[j].z, xr[b][m0 + j].z, acc[b][2]);
+                            acc[b][3] = fmaf(h[j].w, xr[b][m0 + j].w, acc[b][3]);
+                        }
                     }
-                }
+            }
             float tot[B];
 #pragma unroll
             for (int b = 0; b < B; ++b) tot[b] = warp_sum_f32((acc[b][0] + acc[b][1]) + (acc[b][2] + acc[b][3]));
@@ -305,12 +317,9 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
                 // the C per-CTA sums in rank order: the same additions in every thread of the cluster
                 float fitv = 0.f;
                 const uint32_t cd = cdot_u32 + (fin_slot * B + b) * (CSTRIDE * 4);
-                for (uint32_t q = 0; q < c4; ++q) {
+                for (uint32_t q = 0; q < c4; ++q) {  // slots of ranks >= C hold zeros
                     const float4 v = lds128(cd + q * 16);
-                    fitv += v.x;
-                    if (4 * q + 1 < C) fitv += v.y;
-                    if (4 * q + 2 < C) fitv += v.z;
-                    if (4 * q + 3 < C) fitv += v.w;
+                    fitv = (((fitv + v.x) + v.y) + v.z) + v.w;
                 }
                 wi[b] = 0.f;
                 if (gi[b] >= 0.f) wi[b] = a.log_mode ? fitv * ri : (gi[b] - fitv) * ri;
@@ -318,17 +327,23 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             }
             const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
 #pragma unroll
-            for (int m = 0; m < K; ++m)
-                if (m < mine) {
-                    const float4 h = lds128(base + m * (NT * 16));
+            for (int m0 = 0; m0 < K; m0 += G) {
+                float4 h[G];
 #pragma unroll
-                    for (int b = 0; b < B; ++b) {
-                        sacc[b][m].x = fmaf(h.x, wi[b], sacc[b][m].x);
-                        sacc[b][m].y = fmaf(h.y, wi[b], sacc[b][m].y);
-                        sacc[b][m].z = fmaf(h.z, wi[b], sacc[b][m].z);
-                        sacc[b][m].w = fmaf(h.w, wi[b], sacc[b][m].w);
+                for (int j = 0; j < G; ++j)
+                    if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
+#pragma unroll
+                for (int j = 0; j < G; ++j)
+                    if (m0 + j < K) {
+#pragma unroll
+                        for (int b = 0; b < B; ++b) {
+                            sacc[b][m0 + j].x = fmaf(h[j].x, wi[b], sacc[b][m0 + j].x);
+                            sacc[b][m0 + j].y = fmaf(h[j].y, wi[b], sacc[b][m0 + j].y);
+                            sacc[b][m0 + j].z = fmaf(h[j].z, wi[b], sacc[b][m0 + j].z);
+                            sacc[b][m0 + j].w = fmaf(h[j].w, wi[b], sacc[b][m0 + j].w);
+                        }
                     }
-                }
+            }
             __syncwarp();
             if (lane == 0) mbar_arrive(empty_u32 + 8 * fin_stage);
             if (++fin_stage == S) fin_stage = 0;
@@ -338,19 +353,24 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
             }
         };
 
-        // prologue: the first D rows go through FP; then FP(t + D) ; FIN(t) ; shift the queue
+        // prologue: the first D rows go through FP; then per row: FP(t + D) ; FIN(t)
+        load_batch(0);
 #pragma unroll
         for (int d = 0; d < D; ++d)
-            if ((uint32_t)d < n) forward(g_q[d], r_q[d]);
+            if ((uint32_t)d < n) forward();
         for (uint32_t t = 0; t < n; ++t) {
-            if (t + D < n) forward(g_q[D], r_q[D]);
-            finish(g_q[0], r_q[0]);
+            if ((t & 31) == 0) {
+                r_cur = r_nxt;
 #pragma unroll
-            for (int d = 0; d < D; ++d) {
-                r_q[d] = r_q[d + 1];
-#pragma unroll
-                for (int b = 0; b < B; ++b) g_q[d][b] = g_q[d + 1][b];
+                for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
+                load_batch(t + 32);
             }
+            float gi[B];
+#pragma unroll
+            for (int b = 0; b < B; ++b) gi[b] = __shfl_sync(FULL_MASK, g_cur[b], t & 31);
+            const float ri = __shfl_sync(FULL_MASK, r_cur, t & 31);
+            if (t + D < n) forward();
+            finish(gi, ri);
         }
 
 #pragma unroll
