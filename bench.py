@@ -232,7 +232,7 @@ def run_engine_arm(args, cp):
     torch.cuda.synchronize()
     cp.barrier()
     w0 = time.perf_counter()
-    dev_ms, launches, fp_ms, bp_ms, fu_ms, fp_n, bp_n, fu_n = 0.0, 0, 0.0, 0.0, 0.0, 0, 0, 0
+    dev_ms, launches, fp_ms, bp_ms, fu_ms, fp_n, bp_n, fu_n, solve_n = 0.0, 0, 0.0, 0.0, 0.0, 0, 0, 0, 0
     for _ in range(args.steps):
         s = resident_step()
         dev_ms += s.solve_ms
@@ -243,6 +243,7 @@ def run_engine_arm(args, cp):
         fp_n += s.fp_launches
         bp_n += s.bp_launches
         fu_n += s.fused_launches
+        solve_n += s.solve_launches
         tail_ms = s.tail_ms_avg
     torch.cuda.synchronize()  # (every step already ended with an event sync on the engine's own stream)
     sweep_mode = {1: "split", 2: "fused"}.get(s.sweep_mode, "?")
@@ -283,6 +284,12 @@ def run_engine_arm(args, cp):
         "bp_cols_kernel": {"ms": bp_ms / max(bp_n, 1), "launches": bp_n, "algorithmic_bytes": shard_bytes, "hbm_bytes": shard_bytes},
         "fused_sweep_kernel": {"ms": fu_ms / max(fu_n, 1), "launches": fu_n, "algorithmic_bytes": 2 * shard_bytes, "hbm_bytes": shard_bytes},
     }
+    if solve_n:
+        # the whole solve ran as ONE launch per step (fused_solve_kernel): fu_n counts the sweeps inside those launches
+        per = fu_n / solve_n
+        kern.pop("fused_sweep_kernel")
+        kern["fused_solve_kernel"] = {"ms": fu_ms / solve_n, "launches": solve_n, "sweeps_per_launch": per,
+                                      "algorithmic_bytes": 2 * shard_bytes * per, "hbm_bytes": shard_bytes * per}
     for k in kern.values():
         k["gbs"] = k["algorithmic_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else 0.0
         k["hbm_gbs"] = k["hbm_bytes"] / (k["ms"] * 1e-3) / 1e9 if k["ms"] > 0 else 0.0
@@ -296,7 +303,9 @@ def run_engine_arm(args, cp):
         "hbm_frac": kern[dom]["hbm_gbs"] / peak,
         "note": ("fused sweep: algorithmic bytes are the two sweeps of an iteration (2*P*V*4); the kernel reads the shard from "
                  "HBM once and re-reads it from shared memory, so achieved/peak can exceed 1 while hbm_frac cannot"
-                 if dom == "fused_sweep_kernel" else "one sweep of the shard per launch"),
+                 + ("; one launch = all sweeps of a solve (cluster reduction, decision and update between grid barriers inside)"
+                    if dom == "fused_solve_kernel" else "")
+                 if dom.startswith("fused_") else "one sweep of the shard per launch"),
         "kernels": kern,
         "iteration_roofline_frac": (2.0 * shard_bytes * (value / 1.0) / 1e9) / peak,  # 2*bytes(A) per iteration / peak
     }

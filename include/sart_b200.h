@@ -95,11 +95,13 @@ typedef struct sart_stats {
     uint64_t matrix_bytes;   /* npixel_local * nvoxel * 4: algorithmic bytes of ONE sweep of this shard */
     uint64_t h2d_bytes;      /* host->device bytes moved by the last solve */
     uint64_t d2h_bytes;      /* device->host bytes moved by the last solve */
-    double fused_ms_avg;     /* mean duration of one fused forward+back projection launch (SART_SWEEP_FUSED) */
-    int32_t fused_launches;  /* launches behind fused_ms_avg */
+    double fused_ms_avg;     /* mean duration of one fused forward+back projection sweep (SART_SWEEP_FUSED); when the
+                                solve ran as one launch (solve_launches == 1): that launch / fused_launches, i.e.
+                                including what happens between the sweeps */
+    int32_t fused_launches;  /* fused sweeps behind fused_ms_avg (one launch each unless solve_launches == 1) */
     int32_t sweep_mode;      /* SART_SWEEP_SPLIT or SART_SWEEP_FUSED: what the engine runs */
     int32_t exchange_mode;   /* SART_EXCHANGE_*: how the per-iteration reduction over the ranks travels */
-    int32_t reserved;
+    int32_t solve_launches;  /* 1: all sweeps of the solve ran inside ONE cooperative launch (fused_solve_kernel), 0: a launch per sweep */
     double tail_ms_avg;      /* fused sweep: mean device time between two sweeps (reduction over clusters and ranks, decision, update) */
 } sart_stats;
 

@@ -52,7 +52,7 @@ class Stats(C.Structure):
         ("fp_launches", C.c_int32), ("bp_launches", C.c_int32),
         ("matrix_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
         ("fused_ms_avg", C.c_double), ("fused_launches", C.c_int32), ("sweep_mode", C.c_int32),
-        ("exchange_mode", C.c_int32), ("reserved", C.c_int32), ("tail_ms_avg", C.c_double),
+        ("exchange_mode", C.c_int32), ("solve_launches", C.c_int32), ("tail_ms_avg", C.c_double),
     ]
 
 

@@ -116,6 +116,11 @@ struct sart_engine {
     uint32_t fu_cluster = 0, fu_wc = 0, fu_stages = 0, fu_stage_bytes = 0, fu_smem = 0, fu_nclusters = 0;
     void (*fu_kernel)(const sart::FusedArgs) = nullptr;
     uint32_t fu_threads = 0;
+    // whole solve in one cooperative launch (fused_solve_kernel); falls back to one launch per sweep when unavailable
+    bool persistent = false;
+    void (*fs_kernel)(const sart::FusedArgs, const sart::SolveArgs) = nullptr;
+    unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer
+    uint64_t xchg_cta_flag_off = 0;             // per-CTA flags of the in-kernel exchange inside a region
 
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
     cudaEvent_t ev_batch[2] = {nullptr, nullptr};
@@ -248,6 +253,13 @@ FusedKernel pick_fused_kernel(int k, int depth) {
     else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 1, 3> : fused_sweep_kernel<kFusedThreads, K, 1, 1>;
     else return pick_fused_kernel<K + 1>(k, depth);
 }
+typedef void (*SolveKernel)(const FusedArgs, const SolveArgs);
+template <int K>
+SolveKernel pick_solve_kernel(int k, int depth) {
+    if constexpr (K > kFusedKMax) return nullptr;
+    else if (k <= K) return depth == 3 ? fused_solve_kernel<kFusedThreads, K, 3> : fused_solve_kernel<kFusedThreads, K, 1>;
+    else return pick_solve_kernel<K + 1>(k, depth);
+}
 // two frames per sweep: twice the register slices, so at most 4 float4 columns per thread
 constexpr int kFusedKMaxPair = 4;
 template <int K>
@@ -292,7 +304,7 @@ int plan_fused(sart_engine* e) {
     for (uint32_t s = s_cap; s >= 2; --s) {
         // stages + warp partials [2S][NWC] + per-CTA sums [2S][16] + barriers full[S], empty[S], wbar[2S], dot[2S]
         const uint64_t need = (uint64_t)s * stage_bytes + (uint64_t)2 * s * nw * 4 + (uint64_t)2 * s * 16 * 4 + (uint64_t)6 * s * 8;
-        if (need <= (uint64_t)max_smem) {
+        if (need + 256 <= (uint64_t)max_smem) {  // + the kernel's static shared variables
             S = s;
             smem = (uint32_t)need;
             break;
@@ -335,6 +347,23 @@ int plan_fused(sart_engine* e) {
     e->fu_smem = smem;
     e->fu_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
     e->fused = true;
+
+    // whole solve in one cooperative launch, when the device can co-schedule the same grid for that kernel
+    e->persistent = false;
+    int coop = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, e->device));
+    if (coop && env_int("SART_PERSISTENT", 1) != 0) {
+        const SolveKernel sk = pick_solve_kernel<1>(k_need, fused_depth(S));
+        int ncl2 = 0;
+        if (sk && cudaFuncSetAttribute(sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
+            (C <= 8 || cudaFuncSetAttribute(sk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
+            cudaOccupancyMaxActiveClusters(&ncl2, sk, &cfg) == cudaSuccess && ncl2 >= (int)e->fu_nclusters) {
+            e->fs_kernel = sk;
+            e->persistent = true;
+            if (!e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 4));
+        }
+        (void)cudaGetLastError();
+    }
     return SART_OK;
 }
 
@@ -478,6 +507,75 @@ int launch_xchg_update(sart_engine* e, int t, const IterState* st_in, IterState*
     return SART_OK;
 }
 
+// The whole solve (sweeps 0 .. stop) in ONE cooperative launch of fused_solve_kernel: reduction over clusters and ranks,
+// decision and update run inside the kernel between two grid barriers. cudaErrorCooperativeLaunchTooLarge or an
+// unsupported attribute combination is reported as "not launched" so that the caller can fall back.
+int launch_solve(sart_engine* e, bool* launched) {
+    *launched = false;
+    FusedArgs a;
+    a.H = e->dH;
+    a.ld4 = e->ld4;
+    a.P = e->P;
+    a.x = nullptr;
+    a.g = e->d_g;
+    a.rinv = e->d_rinv;
+    a.part = e->d_part;
+    a.f2part = e->d_f2part;
+    a.st = nullptr;
+    a.x_stride = a.g_stride = a.part_stride = a.f2_stride = 0;
+    a.Wc = e->fu_wc;
+    a.stages = e->fu_stages;
+    a.stage_bytes = e->fu_stage_bytes;
+    a.log_mode = e->cfg.logarithmic;
+    SolveArgs sv;
+    for (int k = 0; k < 2; ++k) {
+        sv.st[k] = e->d_st[k];
+        sv.xf[k] = e->d_xf[k];
+        sv.xd[k] = e->d_xd[k];
+    }
+    sv.upd = make_update_args(e, 0, nullptr);
+    sv.tol = e->cfg.conv_tolerance;
+    sv.max_iter = e->cfg.max_iterations;
+    sv.fixed = e->cfg.fixed_iterations;
+    sv.gbar = e->d_solve_ctl;
+    sv.tail_ns = e->d_solve_ctl + 1;
+    sv.V = e->V;
+    sv.ld = e->ld;
+    const bool multi = e->cfg.nranks > 1;
+    sv.peers = multi ? e->d_peers : nullptr;
+    sv.nranks = (uint32_t)e->cfg.nranks;
+    sv.rank = (uint32_t)e->cfg.rank;
+    sv.epoch0 = e->xchg_epoch;
+    sv.buf_off[0] = e->xchg_buf_off[0];
+    sv.buf_off[1] = e->xchg_buf_off[1];
+    sv.flag_off = e->xchg_cta_flag_off;
+    CUDA_TRY(cudaMemsetAsync(e->d_solve_ctl, 0, 4 * sizeof(unsigned long long), e->stream));
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = e->fu_cluster;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeCooperative;
+    attr[1].val.cooperative = 1;
+    cfg.gridDim = dim3(e->fu_cluster * e->fu_nclusters, 1, 1);
+    cfg.blockDim = dim3(e->fu_threads, 1, 1);
+    cfg.dynamicSmemBytes = e->fu_smem;
+    cfg.stream = e->stream;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    const cudaError_t err = cudaLaunchKernelEx(&cfg, e->fs_kernel, a, sv);
+    if (err == cudaErrorCooperativeLaunchTooLarge || err == cudaErrorNotSupported || err == cudaErrorInvalidValue ||
+        err == cudaErrorInvalidConfiguration) {
+        (void)cudaGetLastError();
+        return SART_OK;
+    }
+    CUDA_TRY(err);
+    ++e->launches;
+    *launched = true;
+    return SART_OK;
+}
+
 int launch_decide(sart_engine* e, int t, const double* f2, uint32_t n, const IterState* st_in, IterState* st_out,
                   const FrameScalars* fs = nullptr) {
     DecideArgs d;
@@ -575,6 +673,47 @@ int launch_prepare(sart_engine* e, int weights_mode) {
     return SART_OK;
 }
 
+// What follows the whole-solve kernel: final state to the host, un-normalised solution, statistics.
+int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks) {
+    if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][3], e->stream));
+    unsigned long long tail[2] = {0, 0};
+    CUDA_TRY(cudaMemcpyAsync(&e->h_st[0], e->d_st[0], sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(&e->h_st[1], e->d_solve_ctl + 1, sizeof(tail), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaEventRecord(e->ev_batch[0], e->stream));
+    CUDA_TRY(cudaEventSynchronize(e->ev_batch[0]));
+    const IterState fin = e->h_st[0];
+    std::memcpy(tail, &e->h_st[1], sizeof(tail));
+    if (!fin.done) return fail(SART_ERR_STATE, "whole-solve kernel ended without a decision (internal error)");
+    if (fin.status == kStatusExchangeTimeout)
+        return fail(SART_ERR_NCCL, "in-kernel barrier or peer-memory exchange timed out: a CTA or a rank of the job did not arrive");
+    if (e->cfg.nranks > 1) e->xchg_epoch += (unsigned long long)fin.iterations + 1;  // one exchange per sweep, every rank alike
+
+    finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_xd[0], e->d_xd[1], e->d_st[0], e->d_fs, e->d_xio, e->V);
+    CUDA_TRY(cudaGetLastError());
+    ++e->launches;
+
+    const int nsweeps = fin.iterations + 1;  // sweeps 0 .. iterations, all of them inside the one launch
+    e->stats.status = fin.status;
+    e->stats.iterations = fin.iterations;
+    e->stats.sweeps = sweeps_before + 2 * fin.iterations + 1;
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_it0, e->ev_batch[0]));
+    e->stats.iterate_ms = ms;
+    e->stats.fp_ms_avg = e->stats.bp_ms_avg = 0;
+    e->stats.fp_launches = e->stats.bp_launches = 0;
+    e->stats.fused_ms_avg = 0;
+    e->stats.fused_launches = nsweeps;
+    e->stats.solve_launches = 1;
+    e->stats.tail_ms_avg = tail[1] ? 1e-6 * (double)tail[0] / (double)tail[1] : 0;
+    e->stats.sweep_mode = SART_SWEEP_FUSED;
+    e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE : SART_EXCHANGE_PEER;
+    if (e->profiling) {
+        CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_prof[0][2], e->ev_prof[0][3]));
+        e->stats.fused_ms_avg = ms / nsweeps;  // per sweep, in-kernel tails included
+    }
+    return SART_OK;
+}
+
 // The whole solve from device-resident inputs (d_gd, and d_xio when has_guess) to device-resident output (d_xio).
 int run_solve(sart_engine* e, int has_guess) {
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
@@ -614,6 +753,14 @@ int run_solve(sart_engine* e, int has_guess) {
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
+
+    if (e->fused && e->persistent && (e->cfg.nranks <= 1 || e->peer_exchange)) {
+        bool launched = false;
+        if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][2], e->stream));
+        SART_TRY(launch_solve(e, &launched));
+        if (launched) return finish_persistent_solve(e, sweeps, vblocks);
+        e->persistent = false;  // this device / driver refuses the launch: one launch per sweep from now on
+    }
 
     // Sweeps t = 0 .. max_iterations. Batches are enqueued one ahead of the status poll, so the device never
     // waits for the host; launches that arrive after the device has decided to stop return immediately.
@@ -659,6 +806,7 @@ int run_solve(sart_engine* e, int has_guess) {
     e->stats.fp_launches = e->stats.bp_launches = 0;
     e->stats.fused_ms_avg = 0;
     e->stats.fused_launches = 0;
+    e->stats.solve_launches = 0;
     e->stats.tail_ms_avg = 0;
     e->stats.sweep_mode = e->fused ? SART_SWEEP_FUSED : SART_SWEEP_SPLIT;
     e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE
@@ -734,7 +882,7 @@ int plan_pair(sart_engine* e) {
     uint32_t S = 0, smem = 0;
     for (uint32_t st = 8; st >= 2; --st) {
         const uint64_t need = (uint64_t)st * stage_bytes + (uint64_t)2 * st * 2 * nw * 4 + (uint64_t)2 * st * 2 * 16 * 4 + (uint64_t)6 * st * 8;
-        if (need <= (uint64_t)max_smem) {
+        if (need + 256 <= (uint64_t)max_smem) {  // + the kernel's static shared variables
             S = st;
             smem = (uint32_t)need;
             break;
@@ -1005,8 +1153,13 @@ int setup_peer_exchange(sart_engine* e) {
     NcclApi* api = nccl_api();
     const char* mode = std::getenv("SART_EXCHANGE");
     int ok = !(mode && std::string(mode) == "nccl") && e->cfg.nranks <= kMaxPeers;
-    const uint64_t flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
-    const uint64_t buf_bytes = ceil_div((e->V + 2) * sizeof(double), 256) * 256;
+    // [one flag per rank, 128 B apart][one flag per rank and CTA of the whole-solve kernel][buffer 0][buffer 1]
+    // a buffer holds V + 1 doubles (per-sweep kernels) or one record [sum(fit^2)][chunk] per CTA (whole-solve kernel)
+    const uint64_t nblk = std::max<uint64_t>((uint64_t)e->fu_cluster * e->fu_nclusters, 1);
+    const uint64_t rank_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
+    const uint64_t flags_bytes = rank_flags_bytes + ceil_div((uint64_t)e->cfg.nranks * nblk * 8, 256) * 256;
+    const uint64_t buf_bytes = ceil_div((e->V + 2 * nblk + 2) * sizeof(double), 256) * 256;
+    e->xchg_cta_flag_off = rank_flags_bytes;
     e->xchg_buf_off[0] = flags_bytes;
     e->xchg_buf_off[1] = flags_bytes + buf_bytes;
 
@@ -1049,18 +1202,21 @@ int setup_peer_exchange(sart_engine* e) {
         e->peer_mappings[r] = p;
         peers[r] = static_cast<char*>(p);
     }
-    // adopt the peer path only if every rank managed to map every region
+    // adopt the peer path only if every rank managed to map every region, and the whole-solve kernel only if every
+    // rank can run it with the same grid (the voxel chunks of the in-kernel exchange are per CTA)
     double* d_ok = nullptr;
-    SART_TRY(dev_alloc(&d_ok, 1, false));
-    const double mine_ok = ok ? 1.0 : 0.0;
-    double all_ok = 0.0;
-    CUDA_TRY(cudaMemcpyAsync(d_ok, &mine_ok, sizeof(double), cudaMemcpyHostToDevice, e->stream));
-    NCCL_TRY(api, api->AllReduce(d_ok, d_ok, 1, ncclDouble, ncclMin, e->comm, e->stream));
-    CUDA_TRY(cudaMemcpyAsync(&all_ok, d_ok, sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+    SART_TRY(dev_alloc(&d_ok, 4, false));
+    const double mine_ok[4] = {ok ? 1.0 : 0.0, (e->fused && e->persistent) ? 1.0 : 0.0, (double)nblk, -(double)nblk};
+    double all_ok[4] = {0, 0, 0, 0};
+    CUDA_TRY(cudaMemcpyAsync(d_ok, mine_ok, sizeof(mine_ok), cudaMemcpyHostToDevice, e->stream));
+    NCCL_TRY(api, api->AllReduce(d_ok, d_ok, 4, ncclDouble, ncclMin, e->comm, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(all_ok, d_ok, sizeof(all_ok), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     CUDA_TRY(cudaFree(d_ok));
-    if (all_ok < 0.5) {
+    if (all_ok[1] < 0.5 || all_ok[2] != -all_ok[3]) e->persistent = false;
+    if (all_ok[0] < 0.5) {
         e->peer_exchange = false;
+        e->persistent = false;  // the whole-solve kernel has no NCCL variant
         return SART_OK;
     }
     SART_TRY(dev_alloc(&e->d_peers, (uint64_t)n, false));
@@ -1082,6 +1238,7 @@ void free_engine(sart_engine* e) {
         if (p) cudaIpcCloseMemHandle(p);
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
+    if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
     void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
                          e->d_pg, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
     for (void* p : pair_ptrs)

@@ -138,29 +138,108 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
     return v;
 }
 
+// ---- whole solve in one launch --------------------------------------------------------------------------------------
+// With PERSIST the kernel does not return after the sweep: every CTA of the grid is resident (the grid is sized by
+// cudaOccupancyMaxActiveClusters and launched cooperatively), so the sweeps of one solve are separated by two grid
+// barriers instead of three kernel boundaries, and what the separate kernels did in between runs in the same CTAs:
+//     sweep t (both projections)                                        -> per-cluster partials of s and sum(fit^2)
+//     grid barrier
+//     tail: CTA b owns voxels [b * chunk, (b + 1) * chunk): adds the clusters' partials in fixed order (fp64), with
+//           several ranks publishes that to the peers and adds the ranks' values in rank order (NVLink peer memory,
+//           one flag per CTA and rank: a CTA starts as soon as ITS chunk is complete everywhere), takes the
+//           stop / continue decision (every CTA of every rank computes the same one from the same numbers in the same
+//           order) and writes x_{t+1} for its voxels
+//     grid barrier                                                       -> x_{t+1} visible to every CTA
+// The arithmetic and its order are those of reduce_partials_kernel, decide_kernel, update_kernel and
+// xchg_decide_update_kernel, so both ways of running a solve give bit-identical results.
+// Everything a later sweep reads that an earlier tail wrote goes through L2 (ld.global.cg / .cv): L1 is not coherent
+// within a launch. A barrier or a peer that does not arrive within ~4 s ends the solve with SART_STATUS_EXCHANGE_TIMEOUT.
+struct SolveArgs {
+    IterState* st[2];      // [0] is read on entry; the final state is written to both copies
+    float* xf[2];          // fp32 iterate: sweep t reads xf[t & 1], its tail writes xf[(t + 1) & 1]
+    double* xd[2];         // fp64 master copy, same parity rule
+    UpdArgs upd;           // constant fields of the update (xd_cur / xd_next / xf_next / sred / st are set per sweep)
+    double tol;
+    int max_iter, fixed;
+    unsigned long long* gbar;  // grid barrier counter, zero at launch
+    uint64_t V, ld;
+    char* const* peers;    // [nranks] exchange regions as mapped here, null with one rank
+    uint32_t nranks, rank;
+    unsigned long long epoch0;  // sweep t uses epoch0 + t + 1
+    uint64_t buf_off[2];   // byte offsets of the two exchange buffers inside a region
+    uint64_t flag_off;     // byte offset of the per-CTA flags [nranks][gridDim.x] inside a region
+    unsigned long long* tail_ns;  // [3], zero at launch: ns CTA 0 spent between the end of a sweep (first grid barrier passed) and the start of the next, how often, scratch
+};
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+constexpr long long kSpinLimit = 8000000000LL;            // ~4 s at 2 GHz
+constexpr unsigned long long kBarrierPoison = 1ull << 40;  // added to the barrier counter by a CTA that gives up
+
+// true: every CTA arrived; false: this or another CTA timed out (the counter is poisoned so nobody waits again)
+__device__ __forceinline__ bool grid_barrier(unsigned long long* ctr, unsigned long long target, int* s_abort) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(ctr, 1ull);
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned long long v;
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(ctr) : "memory");
+            if (v >= kBarrierPoison) {
+                *s_abort = 1;
+                break;
+            }
+            if (v >= target) break;
+            if (clock64() - t0 > kSpinLimit) {
+                atomicAdd(ctr, kBarrierPoison);
+                *s_abort = 1;
+                break;
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    return *s_abort == 0;
+}
+
 // warps 0..NWC-1 consumers, warp NWC TMA producer, warp NWC+1 reducer: 16 warps in all, so that every SM sub-partition
 // holds 4 and a thread may use 128 registers (a 17th warp caps the kernel at 96 and spills).
 // B = frames solved by the same sweep (independent right-hand sides that share the matrix: time series without warm
 // start). The matrix row is loaded once and read twice from shared memory whatever B is; only the FMAs, the register
 // slices of x and s, and the exchanged scalars are per frame.
 // D = software-pipeline depth of the consumers: FP runs D rows ahead of FIN, so the exchange latency of a row (reducer
-// wake-up, DSMEM hop, barrier) is spread over D rows of work. Long rows (50 KB per CTA: 4 stages fit) are HBM-bound
-// with D = 1; short rows (8 stages fit) need D = 3. Requires S >= D + 1 (ring) and 2S >= S + D + 1 (slot reuse, below).
+// wake-up, DSMEM hop, barrier) is spread over D rows of work. Requires S >= D + 1 (ring) and 2S >= S + D + 1 (slot
+// reuse, above).
 // shared memory: [S stages][2S x B x NWC warp partials][2S x B x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
-// All ring / slot / barrier positions advance incrementally (no integer division in the row loop).
-template <int NT, int K, int B, int D>
-__global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
-    if (a.st) {
-        bool all_done = true;
-#pragma unroll
-        for (int b = 0; b < B; ++b) all_done = all_done && a.st[b].done;
-        if (all_done) return;
-    }
+// All ring / slot / barrier positions advance incrementally (no integer division in the row loop) and carry over
+// from one sweep of a PERSIST launch to the next.
+template <int NT, int K, int B, int D, bool PERSIST>
+__device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* sv) {
+    static_assert(!PERSIST || B == 1, "the whole-solve kernel handles one frame");
     constexpr uint32_t NWC = NT / 32;
     constexpr uint32_t CSTRIDE = 16;  // floats per slot of per-CTA sums (cluster size <= 16), 64-byte aligned
     // 128-bit shared loads issued back to back before their FMAs (their latency overlaps); bounded by the register budget
     constexpr int G = (B * K >= 7) ? ((B * K >= 13 || B == 1) ? 1 : 2) : (K < 4 ? K : 4);
     extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ int s_abort;
+    __shared__ double s_f2, s_f2r[kMaxPeers];
+
+    double conv_prev = 0.0;
+    if constexpr (PERSIST) {
+        const IterState s0 = *sv->st[0];
+        if (s0.done) return;
+        conv_prev = s0.conv_prev;
+    } else if (a.st) {
+        bool all_done = true;
+#pragma unroll
+        for (int b = 0; b < B; ++b) all_done = all_done && a.st[b].done;
+        if (all_done) return;
+    }
     const uint32_t S = a.stages;
     const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
     const uint32_t cid = cluster_id_x(), ncl = cluster_count_x();
@@ -182,6 +261,7 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     for (uint32_t i = tid; i < 2 * S * B * CSTRIDE; i += blockDim.x)
         asm volatile("st.shared.f32 [%0], %1;" ::"r"(cdot_u32 + 4 * i), "f"(0.f) : "memory");
     if (tid == 0) {
+        s_abort = 0;
         for (uint32_t s = 0; s < S; ++s) {
             mbar_init(full_u32 + 8 * s, 1);
             mbar_init(empty_u32 + 8 * s, NWC);
@@ -195,194 +275,343 @@ __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs
     cluster_sync_all();
 
     const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;
-    if (warp == NWC) {
-        // ---- producer ------------------------------------------------------------------------------------------------
-        if (lane == 0) {
-            const uint32_t bytes = wcols * 16;
-            const char* src = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
-            const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
-            uint32_t stage = 0, slot = 0, empty_parity = 1;
-            for (uint32_t t = 0; t < n; ++t) {
-                mbar_wait(empty_u32 + 8 * stage, empty_parity);
-                mbar_expect_tx(dot_u32 + 8 * slot, 4 * C * B);  // one float per frame from every CTA of the cluster
-                mbar_expect_tx(full_u32 + 8 * stage, bytes);
-                if (bytes) bulk_load(ring_u32 + stage * a.stage_bytes, src, bytes, full_u32 + 8 * stage);
-                src += src_step;
-                if (++stage == S) {
-                    stage = 0;
-                    empty_parity ^= 1;
-                }
-                if (++slot == 2 * S) slot = 0;
-            }
-        }
-        __syncwarp();
-    } else if (warp == NWC + 1) {
-        // ---- reducer: CTA-level sum of the warp partials, one message per peer (and frame) -------------------------------
-        const uint32_t peer = (lane < C) ? lane : 0;
-        const uint32_t peer_cdot0 = map_to_cta(cdot_u32 + rank * 4, peer);
-        const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
-        uint32_t slot = 0, parity = 0;
-        for (uint32_t t = 0; t < n; ++t) {
-            mbar_wait(wbar_u32 + 8 * slot, parity);
-#pragma unroll
-            for (int b = 0; b < B; ++b) {
-                float p = (lane < NWC) ? lds32(wpart_u32 + ((slot * B + b) * NWC + lane) * 4) : 0.f;
-                p = warp_sum_f32(p);  // fixed tree over the NWC partials
-                if (lane < C) st_async_remote_f32(peer_cdot0 + (slot * B + b) * (CSTRIDE * 4), p, peer_dot0 + 8 * slot);
-            }
-            if (++slot == 2 * S) {
-                slot = 0;
-                parity ^= 1;
-            }
-        }
-        __syncwarp();
-    } else {
-        // ---- consumers -----------------------------------------------------------------------------------------------
-        const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
-        float4 xr[B][K], sacc[B][K];
-#pragma unroll
-        for (int b = 0; b < B; ++b) {
-            const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x + b * a.x_stride) + c0 + tid;
-#pragma unroll
-            for (int m = 0; m < K; ++m) {
-                xr[b][m] = (m < mine) ? __ldg(x4 + m * NT) : make_float4(0.f, 0.f, 0.f, 0.f);
-                sacc[b][m] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
-        double f2acc[B];
-#pragma unroll
-        for (int b = 0; b < B; ++b) f2acc[b] = 0.0;
-        uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0;
-        uint32_t fin_stage = 0, fin_slot = 0, fin_parity = 0;
-        // Measurements and inverse ray lengths of the cluster's rows are fetched 32 rows at a time: lane l holds row
-        // 32j + l of batch j, the batch after the current one is already in flight, and each row's values are
-        // broadcast with a shuffle. A per-row load, however early it is issued, ends up waited for within the row
-        // (its register is touched when the pipeline queue shifts), which put one exposed L2/HBM latency on every
-        // row and capped short rows at ~0.75 us each.
-        float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
-        auto load_batch = [&](uint32_t t0) {
-            const uint32_t row = t0 + lane;
-            const uint64_t off = (uint64_t)cid + (uint64_t)row * ncl;
-#pragma unroll
-            for (int b = 0; b < B; ++b) g_nxt[b] = (row < n) ? __ldg(a.g + b * a.g_stride + off) : 0.f;
-            r_nxt = (row < n) ? __ldg(a.rinv + off) : 0.f;
-        };
-        const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
+    // ring / slot positions of the three roles; they run on from sweep to sweep
+    uint32_t pr_stage = 0, pr_slot = 0, pr_parity = 1;                                    // producer
+    uint32_t rd_slot = 0, rd_parity = 0;                                                  // reducer
+    uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0, fin_stage = 0, fin_slot = 0, fin_parity = 0;  // consumers
+    unsigned long long bar_target = 0;
 
-        auto forward = [&]() {
-            mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
-            const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
-            float acc[B][4];
-#pragma unroll
-            for (int b = 0; b < B; ++b) acc[b][0] = acc[b][1] = acc[b][2] = acc[b][3] = 0.f;
-#pragma unroll
-            for (int m0 = 0; m0 < K; m0 += G) {
-                float4 h[G];
-#pragma unroll
-                for (int j = 0; j < G; ++j)
-                    if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
-#pragma unroll
-                for (int j = 0; j < G; ++j)
-                    if (m0 + j < K) {
-#pragma unroll
-                        for (int b = 0; b < B; ++b) {
-                            acc[b][0] = fmaf(h[j].x, xr[b][m0 + j].x, acc[b][0]);
-                            acc[b][1] = fmaf(h[j].y, xr[b][m0 + j].y, acc[b][1]);
-                            acc[b][2] = fmaf(h[j].z, xr[b][m0 + j].z, acc[b][2]);
-                            acc[b][3] = fmaf(h[j].w, xr[b][m0 + j].w, acc[b][3]);
-                        }
-                    }
-            }
-            float tot[B];
-#pragma unroll
-            for (int b = 0; b < B; ++b) tot[b] = warp_sum_f32((acc[b][0] + acc[b][1]) + (acc[b][2] + acc[b][3]));
+    for (int t = 0;; ++t) {
+        const float* xcur = a.x;
+        if constexpr (PERSIST) xcur = sv->xf[t & 1];
+
+        if (warp == NWC) {
+            // ---- producer --------------------------------------------------------------------------------------------
             if (lane == 0) {
-#pragma unroll
-                for (int b = 0; b < B; ++b)
-                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + ((fp_slot * B + b) * NWC + warp) * 4), "f"(tot[b]) : "memory");
-                mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partials
-            }
-            if (++fp_stage == S) {
-                fp_stage = 0;
-                fp_parity ^= 1;
-            }
-            if (++fp_slot == 2 * S) fp_slot = 0;
-        };
-
-        auto finish = [&](const float (&gi)[B], float ri) {
-            mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
-            float wi[B];
-#pragma unroll
-            for (int b = 0; b < B; ++b) {
-                // the C per-CTA sums in rank order: the same additions in every thread of the cluster
-                float fitv = 0.f;
-                const uint32_t cd = cdot_u32 + (fin_slot * B + b) * (CSTRIDE * 4);
-                for (uint32_t q = 0; q < c4; ++q) {  // slots of ranks >= C hold zeros
-                    const float4 v = lds128(cd + q * 16);
-                    fitv = (((fitv + v.x) + v.y) + v.z) + v.w;
-                }
-                wi[b] = 0.f;
-                if (gi[b] >= 0.f) wi[b] = a.log_mode ? fitv * ri : (gi[b] - fitv) * ri;
-                f2acc[b] += (double)fitv * (double)fitv;
-            }
-            const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
-#pragma unroll
-            for (int m0 = 0; m0 < K; m0 += G) {
-                float4 h[G];
-#pragma unroll
-                for (int j = 0; j < G; ++j)
-                    if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
-#pragma unroll
-                for (int j = 0; j < G; ++j)
-                    if (m0 + j < K) {
-#pragma unroll
-                        for (int b = 0; b < B; ++b) {
-                            sacc[b][m0 + j].x = fmaf(h[j].x, wi[b], sacc[b][m0 + j].x);
-                            sacc[b][m0 + j].y = fmaf(h[j].y, wi[b], sacc[b][m0 + j].y);
-                            sacc[b][m0 + j].z = fmaf(h[j].z, wi[b], sacc[b][m0 + j].z);
-                            sacc[b][m0 + j].w = fmaf(h[j].w, wi[b], sacc[b][m0 + j].w);
-                        }
+                const uint32_t bytes = wcols * 16;
+                const char* src = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
+                const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
+                for (uint32_t r = 0; r < n; ++r) {
+                    mbar_wait(empty_u32 + 8 * pr_stage, pr_parity);
+                    mbar_expect_tx(dot_u32 + 8 * pr_slot, 4 * C * B);  // one float per frame from every CTA of the cluster
+                    mbar_expect_tx(full_u32 + 8 * pr_stage, bytes);
+                    if (bytes) bulk_load(ring_u32 + pr_stage * a.stage_bytes, src, bytes, full_u32 + 8 * pr_stage);
+                    src += src_step;
+                    if (++pr_stage == S) {
+                        pr_stage = 0;
+                        pr_parity ^= 1;
                     }
+                    if (++pr_slot == 2 * S) pr_slot = 0;
+                }
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(empty_u32 + 8 * fin_stage);
-            if (++fin_stage == S) fin_stage = 0;
-            if (++fin_slot == 2 * S) {
-                fin_slot = 0;
-                fin_parity ^= 1;
+        } else if (warp == NWC + 1) {
+            // ---- reducer: CTA-level sum of the warp partials, one message per peer (and frame) ---------------------------
+            const uint32_t peer = (lane < C) ? lane : 0;
+            const uint32_t peer_cdot0 = map_to_cta(cdot_u32 + rank * 4, peer);
+            const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
+            for (uint32_t r = 0; r < n; ++r) {
+                mbar_wait(wbar_u32 + 8 * rd_slot, rd_parity);
+#pragma unroll
+                for (int b = 0; b < B; ++b) {
+                    float p = (lane < NWC) ? lds32(wpart_u32 + ((rd_slot * B + b) * NWC + lane) * 4) : 0.f;
+                    p = warp_sum_f32(p);  // fixed tree over the NWC partials
+                    if (lane < C) st_async_remote_f32(peer_cdot0 + (rd_slot * B + b) * (CSTRIDE * 4), p, peer_dot0 + 8 * rd_slot);
+                }
+                if (++rd_slot == 2 * S) {
+                    rd_slot = 0;
+                    rd_parity ^= 1;
+                }
             }
-        };
+            __syncwarp();
+        } else {
+            // ---- consumers -------------------------------------------------------------------------------------------
+            const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
+            float4 xr[B][K], sacc[B][K];
+#pragma unroll
+            for (int b = 0; b < B; ++b) {
+                const float4* x4 = reinterpret_cast<const float4*>(xcur + b * a.x_stride) + c0 + tid;
+#pragma unroll
+                for (int m = 0; m < K; ++m) {
+                    // a PERSIST launch reads what the previous tail wrote: through L2, never the read-only path
+                    xr[b][m] = (m < mine) ? (PERSIST ? __ldcg(x4 + m * NT) : __ldg(x4 + m * NT)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    sacc[b][m] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            double f2acc[B];
+#pragma unroll
+            for (int b = 0; b < B; ++b) f2acc[b] = 0.0;
+            // Measurements and inverse ray lengths of the cluster's rows are fetched 32 rows at a time: lane l holds row
+            // 32j + l of batch j, the batch after the current one is already in flight, and each row's values are
+            // broadcast with a shuffle. A per-row load, however early it is issued, ends up waited for within the row
+            // (its register is touched when the pipeline queue shifts), which put one exposed L2/HBM latency on every
+            // row and capped short rows at ~0.75 us each.
+            float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
+            auto load_batch = [&](uint32_t t0) {
+                const uint32_t row = t0 + lane;
+                const uint64_t off = (uint64_t)cid + (uint64_t)row * ncl;
+#pragma unroll
+                for (int b = 0; b < B; ++b) g_nxt[b] = (row < n) ? __ldg(a.g + b * a.g_stride + off) : 0.f;
+                r_nxt = (row < n) ? __ldg(a.rinv + off) : 0.f;
+            };
+            const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
 
-        // prologue: the first D rows go through FP; then per row: FP(t + D) ; FIN(t)
-        load_batch(0);
+            auto forward = [&]() {
+                mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
+                const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
+                float acc[B][4];
 #pragma unroll
-        for (int d = 0; d < D; ++d)
-            if ((uint32_t)d < n) forward();
-        for (uint32_t t = 0; t < n; ++t) {
-            if ((t & 31) == 0) {
-                r_cur = r_nxt;
+                for (int b = 0; b < B; ++b) acc[b][0] = acc[b][1] = acc[b][2] = acc[b][3] = 0.f;
 #pragma unroll
-                for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
-                load_batch(t + 32);
+                for (int m0 = 0; m0 < K; m0 += G) {
+                    float4 h[G];
+#pragma unroll
+                    for (int j = 0; j < G; ++j)
+                        if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
+#pragma unroll
+                    for (int j = 0; j < G; ++j)
+                        if (m0 + j < K) {
+#pragma unroll
+                            for (int b = 0; b < B; ++b) {
+                                acc[b][0] = fmaf(h[j].x, xr[b][m0 + j].x, acc[b][0]);
+                                acc[b][1] = fmaf(h[j].y, xr[b][m0 + j].y, acc[b][1]);
+                                acc[b][2] = fmaf(h[j].z, xr[b][m0 + j].z, acc[b][2]);
+                                acc[b][3] = fmaf(h[j].w, xr[b][m0 + j].w, acc[b][3]);
+                            }
+                        }
+                }
+                float tot[B];
+#pragma unroll
+                for (int b = 0; b < B; ++b) tot[b] = warp_sum_f32((acc[b][0] + acc[b][1]) + (acc[b][2] + acc[b][3]));
+                if (lane == 0) {
+#pragma unroll
+                    for (int b = 0; b < B; ++b)
+                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + ((fp_slot * B + b) * NWC + warp) * 4), "f"(tot[b]) : "memory");
+                    mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partials
+                }
+                if (++fp_stage == S) {
+                    fp_stage = 0;
+                    fp_parity ^= 1;
+                }
+                if (++fp_slot == 2 * S) fp_slot = 0;
+            };
+
+            auto finish = [&](const float (&gi)[B], float ri) {
+                mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
+                float wi[B];
+#pragma unroll
+                for (int b = 0; b < B; ++b) {
+                    // the C per-CTA sums in rank order: the same additions in every thread of the cluster
+                    float fitv = 0.f;
+                    const uint32_t cd = cdot_u32 + (fin_slot * B + b) * (CSTRIDE * 4);
+                    for (uint32_t q = 0; q < c4; ++q) {  // slots of ranks >= C hold zeros
+                        const float4 v = lds128(cd + q * 16);
+                        fitv = (((fitv + v.x) + v.y) + v.z) + v.w;
+                    }
+                    wi[b] = 0.f;
+                    if (gi[b] >= 0.f) wi[b] = a.log_mode ? fitv * ri : (gi[b] - fitv) * ri;
+                    f2acc[b] += (double)fitv * (double)fitv;
+                }
+                const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
+#pragma unroll
+                for (int m0 = 0; m0 < K; m0 += G) {
+                    float4 h[G];
+#pragma unroll
+                    for (int j = 0; j < G; ++j)
+                        if (m0 + j < K) h[j] = lds128(base + (m0 + j) * (NT * 16));
+#pragma unroll
+                    for (int j = 0; j < G; ++j)
+                        if (m0 + j < K) {
+#pragma unroll
+                            for (int b = 0; b < B; ++b) {
+                                sacc[b][m0 + j].x = fmaf(h[j].x, wi[b], sacc[b][m0 + j].x);
+                                sacc[b][m0 + j].y = fmaf(h[j].y, wi[b], sacc[b][m0 + j].y);
+                                sacc[b][m0 + j].z = fmaf(h[j].z, wi[b], sacc[b][m0 + j].z);
+                                sacc[b][m0 + j].w = fmaf(h[j].w, wi[b], sacc[b][m0 + j].w);
+                            }
+                        }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty_u32 + 8 * fin_stage);
+                if (++fin_stage == S) fin_stage = 0;
+                if (++fin_slot == 2 * S) {
+                    fin_slot = 0;
+                    fin_parity ^= 1;
+                }
+            };
+
+            // prologue: the first D rows go through FP; then per row: FP(r + D) ; FIN(r)
+            load_batch(0);
+#pragma unroll
+            for (int d = 0; d < D; ++d)
+                if ((uint32_t)d < n) forward();
+            for (uint32_t r = 0; r < n; ++r) {
+                if ((r & 31) == 0) {
+                    r_cur = r_nxt;
+#pragma unroll
+                    for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
+                    load_batch(r + 32);
+                }
+                float gi[B];
+#pragma unroll
+                for (int b = 0; b < B; ++b) gi[b] = __shfl_sync(FULL_MASK, g_cur[b], r & 31);
+                const float ri = __shfl_sync(FULL_MASK, r_cur, r & 31);
+                if (r + D < n) forward();
+                finish(gi, ri);
             }
-            float gi[B];
+
 #pragma unroll
-            for (int b = 0; b < B; ++b) gi[b] = __shfl_sync(FULL_MASK, g_cur[b], t & 31);
-            const float ri = __shfl_sync(FULL_MASK, r_cur, t & 31);
-            if (t + D < n) forward();
-            finish(gi, ri);
+            for (int b = 0; b < B; ++b) {
+                float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part + b * a.part_stride) + (uint64_t)cid * a.ld4 + c0 + tid;
+#pragma unroll
+                for (int m = 0; m < K; ++m)
+                    if (m < mine) out4[m * NT] = sacc[b][m];
+                if (rank == 0 && tid == 0) a.f2part[b * a.f2_stride + cid] = f2acc[b];
+            }
         }
-
+        if constexpr (!PERSIST) {
+            break;
+        } else {
+            // ---- tail of sweep t ----------------------------------------------------------------------------------------
+            const uint32_t nblk = gridDim.x, blk = blockIdx.x;
+            bar_target += nblk;
+            bool ok = grid_barrier(sv->gbar, bar_target, &s_abort);
+            if (blk == 0 && tid == 0) sv->tail_ns[2] = global_timer_ns();  // the slowest cluster has finished its rows
+            const uint64_t V = sv->V, chunk = (V + nblk - 1) / nblk;
+            const uint64_t j0 = min(V, (uint64_t)blk * chunk), j1 = min(V, j0 + chunk);
+            // this rank's partial of voxel j: the clusters' partials in fixed order (reduce_partials_kernel)
+            auto local_sum = [&](uint64_t j) {
+                double sj = 0.0;
+                for (uint32_t k0 = 0; k0 < ncl; k0 += 8) {  // eight L2 loads in flight, added in cluster order
+                    float v[8];
 #pragma unroll
-        for (int b = 0; b < B; ++b) {
-            float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part + b * a.part_stride) + (uint64_t)cid * a.ld4 + c0 + tid;
+                    for (uint32_t i = 0; i < 8; ++i) v[i] = (k0 + i < ncl) ? __ldcg(a.part + (uint64_t)(k0 + i) * sv->ld + j) : 0.f;
 #pragma unroll
-            for (int m = 0; m < K; ++m)
-                if (m < mine) out4[m * NT] = sacc[b][m];
-            if (rank == 0 && tid == 0) a.f2part[b * a.f2_stride + cid] = f2acc[b];
+                    for (uint32_t i = 0; i < 8; ++i) sj += (double)v[i];
+                }
+                return sj;
+            };
+            if (ok && warp == 0) {
+                double f = 0.0;
+                for (uint32_t k = lane; k < ncl; k += 32) f += __ldcg(a.f2part + k);
+                f = warp_sum(f);
+                if (lane == 0) s_f2 = f;
+            }
+            const bool multi = sv->nranks > 1;
+            const unsigned long long epoch = sv->epoch0 + (unsigned long long)t + 1;
+            const uint64_t rec = (uint64_t)blk * (chunk + 1);  // this CTA's record in an exchange buffer: [sum(fit^2)][chunk]
+            if (ok && multi) {
+                double* mine = reinterpret_cast<double*>(sv->peers[sv->rank] + sv->buf_off[epoch & 1]) + rec;
+                for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) mine[1 + (j - j0)] = local_sum(j);
+                __syncthreads();  // s_f2, and this CTA's record complete
+                if (tid == 0) mine[0] = s_f2;
+                __threadfence_system();
+                __syncthreads();
+                if (tid < sv->nranks) {
+                    const uint64_t fl = sv->flag_off + ((uint64_t)sv->rank * nblk + blk) * 8;
+                    st_release_sys_u64(reinterpret_cast<unsigned long long*>(sv->peers[tid] + fl), epoch);
+                    const unsigned long long* flag = reinterpret_cast<const unsigned long long*>(
+                        sv->peers[sv->rank] + sv->flag_off + ((uint64_t)tid * nblk + blk) * 8);
+                    const long long t0 = clock64();
+                    while (ld_acquire_sys_u64(flag) < epoch) {
+                        if (clock64() - t0 > kSpinLimit) {
+                            s_abort = 1;
+                            break;
+                        }
+                    }
+                    s_f2r[tid] = __ldcv(reinterpret_cast<const double*>(sv->peers[tid] + sv->buf_off[epoch & 1]) + rec);
+                }
+            }
+            __syncthreads();
+            if (s_abort) ok = false;
+            // decision for x_t (decide_kernel / xchg_decide_update_kernel): identical in every CTA of every rank
+            bool stop = false;
+            int status = 0;
+            if (!ok) {
+                atomicAdd(sv->gbar, kBarrierPoison);  // nobody waits for this CTA again
+                stop = true;
+                status = kStatusExchangeTimeout;
+            } else if (t >= 1) {
+                double f2 = s_f2;
+                if (multi) {
+                    f2 = 0.0;
+                    for (uint32_t r = 0; r < sv->nranks; ++r) f2 += s_f2r[r];
+                }
+                const double m2 = sv->upd.fs->m2;
+                const double conv = (m2 - f2) / m2;
+                if (!sv->fixed && t - 1 >= 1 && fabs(conv - conv_prev) < sv->tol) {
+                    stop = true;
+                    status = 0;
+                } else if (t >= sv->max_iter) {
+                    stop = true;
+                    status = -1;
+                }
+                conv_prev = conv;
+            }
+            if (stop) {
+                if ((blk == 0 || !ok) && tid == 0) {
+                    IterState o;
+                    o.conv_prev = conv_prev;
+                    o.k = t;
+                    o.done = 1;
+                    o.status = status;
+                    o.iterations = t;
+                    o.final_buf = t & 1;
+                    o.pad = 0;
+                    *sv->st[0] = o;
+                    *sv->st[1] = o;
+                }
+                break;
+            }
+            UpdArgs u = sv->upd;
+            u.xd_cur = sv->xd[t & 1];
+            u.xd_next = sv->xd[(t + 1) & 1];
+            u.xf_next = sv->xf[(t + 1) & 1];
+            for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) {
+                double sj;
+                if (multi) {
+                    sj = 0.0;
+                    for (uint32_t r = 0; r < sv->nranks; ++r)
+                        sj += __ldcv(reinterpret_cast<const double*>(sv->peers[r] + sv->buf_off[epoch & 1]) + rec + 1 + (j - j0));
+                } else {
+                    sj = local_sum(j);
+                }
+                apply_update(u, j, sj);
+            }
+            bar_target += nblk;
+            if (!grid_barrier(sv->gbar, bar_target, &s_abort)) {
+                if (tid == 0) {
+                    IterState o;
+                    o.conv_prev = conv_prev;
+                    o.k = t;
+                    o.done = 1;
+                    o.status = kStatusExchangeTimeout;
+                    o.iterations = t;
+                    o.final_buf = t & 1;
+                    o.pad = 0;
+                    *sv->st[0] = o;
+                    *sv->st[1] = o;
+                }
+                break;
+            }
+            if (blk == 0 && tid == 0) {
+                sv->tail_ns[0] += global_timer_ns() - sv->tail_ns[2];
+                sv->tail_ns[1] += 1;
+            }
         }
     }
     cluster_sync_all();
+}
+
+template <int NT, int K, int B, int D>
+__global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
+    fused_body<NT, K, B, D, false>(a, nullptr);
+}
+
+// the whole solve: sweeps 0 .. stop in one cooperative launch (one frame)
+template <int NT, int K, int D>
+__global__ void __launch_bounds__(NT + 64, 1) fused_solve_kernel(const FusedArgs a, const SolveArgs sv) {
+    fused_body<NT, K, 1, D, true>(a, &sv);
 }
 
 }  // namespace sart

@@ -358,13 +358,14 @@ struct UpdArgs {
     int log_mode;
 };
 
-// x_{t+1,j} from x_t and the reduced back projection s_j of voxel j
+// x_{t+1,j} from x_t and the reduced back projection s_j of voxel j. x_t is read through L2 (ld.global.cg): in the
+// whole-solve kernel it was written by other SMs earlier in the same launch.
 __device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, double sj) {
     double pen = 0.0;
     if (a.lap_rowptr) {
         const int b = a.lap_rowptr[j], e = a.lap_rowptr[j + 1];
         for (int k = b; k < e; ++k) {
-            const double xv = a.xd_cur[a.lap_col[k]];
+            const double xv = __ldcg(a.xd_cur + a.lap_col[k]);
             pen += a.beta * (double)a.lap_val[k] * (a.log_mode ? log(xv) : xv);
         }
     }
@@ -373,12 +374,12 @@ __device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, doubl
     double xn;
     if (!a.log_mode) {
         const double diff = on ? sj * (a.relax / rho) : 0.0;
-        xn = a.xd_cur[j] + (diff - pen);
+        xn = __ldcg(a.xd_cur + j) + (diff - pen);
         if (signbit(xn)) xn = 0.0;
     } else {
         const double fitj = on ? sj : 0.0;
         const double eps = a.eps_norm + a.eps_orig / a.fs->norm;
-        xn = a.xd_cur[j] * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
+        xn = __ldcg(a.xd_cur + j) * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
     }
     a.xd_next[j] = xn;
     a.xf_next[j] = (float)xn;

@@ -124,9 +124,41 @@ def test_fixed_iterations_parity_across_shapes(P, V, iters, mode, sart, restatem
         s = eng.stats()
     assert (st, it) == (st_ref, it_ref) == (sart.MAX_ITERATIONS_EXCEEDED, iters)
     assert rel_l2(x, x_ref) <= TOL
-    assert s.sweep_mode == mode and s.sweeps == 2 * iters + 2 and s.gpu_launches >= 4 * iters
-    if mode == FUSED:
+    assert s.sweep_mode == mode and s.sweeps == 2 * iters + 2
+    if mode == FUSED and s.solve_launches:
+        # the whole solve ran as one cooperative launch: sweeps 0 .. iters inside it
+        assert s.solve_launches == 1 and s.fused_launches == iters + 1 and s.bp_launches == 0 and s.fp_launches == 0
+    elif mode == FUSED:
         assert s.fused_launches == min(iters, 64) and s.bp_launches == 0 and s.fp_launches == 1
+    else:
+        assert s.gpu_launches >= 4 * iters
+
+
+@pytest.mark.parametrize("P,V,log,tol", [(3000, 4100, 0, 1e-5), (700, 20000, 0, 1e-30), (1500, 9000, 1, 1e-5), (64, 5000, 0, 1e-4)])
+def test_whole_solve_kernel_is_bit_identical_to_one_launch_per_sweep(P, V, log, tol, sart, restatement, monkeypatch):
+    """fused_solve_kernel (all sweeps, cluster reduction, decision and update inside one cooperative launch) repeats the
+    arithmetic of the per-sweep kernels in the same order: same bits, same status, same stopping iteration."""
+    syn = load_synthetic()
+    H = restatement.fill_synthetic(P, V, 123)
+    g = restatement.forward(H, syn.emission_profile(V))
+    if not log:
+        g[::17] = -1.0  # saturated pixels
+    lap = syn.laplacian_coo(V)
+    out = {}
+    for persistent in ("1", "0"):
+        monkeypatch.setenv("SART_PERSISTENT", persistent)
+        with sart.Engine(P, V, device=0, beta_laplace=2e-2, max_iterations=40, conv_tolerance=tol, logarithmic=log,
+                         sweep_mode=FUSED) as eng:
+            eng.upload_rows(H)
+            eng.set_laplacian(*lap)
+            eng.finalize()
+            cold = eng.solve(g)
+            warm = eng.solve(1.5 * g, cold[0])
+            out[persistent] = (cold, warm, eng.stats().solve_launches)
+    assert out["1"][2] == 1 and out["0"][2] == 0
+    for a, b in zip(out["1"][:2], out["0"][:2]):
+        assert a[1:] == b[1:]
+        assert np.array_equal(a[0], b[0])
 
 
 def test_gpu_semantics_masked_initial_guess(sart, restatement):
