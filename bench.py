@@ -53,11 +53,15 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md, 6.65 TB/s)"
 
 
-def profiled_traffic(kernel):
-    """dram bytes per launch of the dominant kernel from the committed ncu capture, if one was summarised."""
+def profiled_traffic(kernel, sweeps_per_launch=1.0):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture, if one was summarised. The
+    whole-solve kernel was captured with 4 sweeps per launch: its figure is kept per sweep and scaled to this run."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel)
+            t = json.load(f)
+        if kernel == "fused_solve_kernel":
+            return int(t["fused_solve_kernel_per_sweep"] * sweeps_per_launch)
+        return t.get(kernel)
     except Exception:
         return None
 
@@ -297,7 +301,7 @@ def run_engine_arm(args, cp):
     dom = max(kern, key=lambda n: kern[n]["ms"] * kern[n]["launches"])
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": kern[dom]["gbs"], "peak": peak, "unit": "GB/s",
-        "frac": kern[dom]["gbs"] / peak, "traffic": profiled_traffic(dom), "peak_source": peak_src,
+        "frac": kern[dom]["gbs"] / peak, "traffic": profiled_traffic(dom, kern[dom].get("sweeps_per_launch", 1.0)), "peak_source": peak_src,
         "algorithmic_bytes_per_launch": kern[dom]["algorithmic_bytes"],
         "hbm_bytes_per_launch": kern[dom]["hbm_bytes"], "hbm_achieved": kern[dom]["hbm_gbs"],
         "hbm_frac": kern[dom]["hbm_gbs"] / peak,

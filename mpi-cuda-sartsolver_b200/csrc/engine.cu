@@ -563,7 +563,11 @@ int launch_solve(sart_engine* e, bool* launched) {
     cfg.dynamicSmemBytes = e->fu_smem;
     cfg.stream = e->stream;
     cfg.attrs = attr;
-    cfg.numAttrs = 2;
+    // SART_COOPERATIVE=0 drops the cooperative attribute (Nsight Compute 2025.2 cannot replay a cooperative cluster
+    // launch: "LaunchFailed"). The grid is the same and still fits the device at once (cudaOccupancyMaxActiveClusters),
+    // but then nothing checks that the GPU is not shared; a CTA that never becomes resident ends the solve through
+    // the barrier timeout instead of a launch error.
+    cfg.numAttrs = env_int("SART_COOPERATIVE", 1) != 0 ? 2 : 1;
     const cudaError_t err = cudaLaunchKernelEx(&cfg, e->fs_kernel, a, sv);
     if (err == cudaErrorCooperativeLaunchTooLarge || err == cudaErrorNotSupported || err == cudaErrorInvalidValue ||
         err == cudaErrorInvalidConfiguration) {
