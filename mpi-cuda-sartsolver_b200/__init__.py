@@ -274,7 +274,7 @@ class Engine:
         return x, st.value, it.value
 
     def solve_batch(self, frames):
-        """Independent frames (no warm start), solved two per matrix sweep where possible.
+        """Independent frames (no warm start), solved four per matrix pass where possible.
         frames [F][nrows] -> (x [F][nvoxel], status [F], iterations [F])."""
         g = np.ascontiguousarray(np.atleast_2d(frames), dtype=np.float64)
         if g.shape[1] != self.nrows:

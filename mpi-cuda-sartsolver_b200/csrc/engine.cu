@@ -135,17 +135,16 @@ struct sart_engine {
     uint64_t xchg_buf_off[2] = {0, 0};
     unsigned long long xchg_epoch = 0;
     bool peer_exchange = false;
-    // two-frames-per-sweep path (sart_solve_batch): geometry + buffers, allocated on first use
-    bool pair_planned = false, pair_ok = false;
-    uint32_t pr_cluster = 0, pr_wc = 0, pr_stages = 0, pr_stage_bytes = 0, pr_smem = 0, pr_nclusters = 0;
-    void (*pr_kernel)(const sart::FusedArgs) = nullptr;
+    // several frames per matrix pass (sart_solve_batch): geometry + buffers for kGroup frames, allocated on first use
+    bool group_planned = false, group_ok = false;
+    uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
     double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr;
-    double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [2][V]
-    float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [2][ld]
-    float *d_pg = nullptr, *d_ppart = nullptr;
-    FrameScalars* d_pfs = nullptr;           // [2]
-    IterState* d_pst[2] = {nullptr, nullptr};  // [parity] -> [2]
-    IterState* h_pst = nullptr;              // pinned, 2 slots x 2 frames
+    double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
+    float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
+    float *d_pg = nullptr, *d_pw = nullptr, *d_ppart = nullptr;
+    FrameScalars* d_pfs = nullptr;           // [kGroup]
+    IterState* d_pst[2] = {nullptr, nullptr};  // [parity] -> [kGroup]
+    IterState* h_pst = nullptr;              // pinned, 2 slots x kGroup frames
     // pinned staging ring of the file loader (allocated on first use)
     static constexpr int kStagingBuffers = 3;
     char* h_staging[kStagingBuffers] = {nullptr, nullptr, nullptr};
@@ -250,7 +249,7 @@ inline int fused_depth(uint32_t stages) {
 template <int K>
 FusedKernel pick_fused_kernel(int k, int depth) {
     if constexpr (K > kFusedKMax) return nullptr;
-    else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 1, 3> : fused_sweep_kernel<kFusedThreads, K, 1, 1>;
+    else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 3> : fused_sweep_kernel<kFusedThreads, K, 1>;
     else return pick_fused_kernel<K + 1>(k, depth);
 }
 typedef void (*SolveKernel)(const FusedArgs, const SolveArgs);
@@ -260,15 +259,6 @@ SolveKernel pick_solve_kernel(int k, int depth) {
     else if (k <= K) return depth == 3 ? fused_solve_kernel<kFusedThreads, K, 3> : fused_solve_kernel<kFusedThreads, K, 1>;
     else return pick_solve_kernel<K + 1>(k, depth);
 }
-// two frames per sweep: twice the register slices, so at most 4 float4 columns per thread
-constexpr int kFusedKMaxPair = 4;
-template <int K>
-FusedKernel pick_fused_pair_kernel(int k, int depth) {
-    if constexpr (K > kFusedKMaxPair) return nullptr;
-    else if (k <= K) return depth == 3 ? fused_sweep_kernel<kFusedThreads, K, 2, 3> : fused_sweep_kernel<kFusedThreads, K, 2, 1>;
-    else return pick_fused_pair_kernel<K + 1>(k, depth);
-}
-
 // Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
 // registers (<= K float4 per thread), as many shared-memory stages of one row panel as fit, and as many clusters as
 // the device can keep resident. Leaves e->fused false when the shape or the device cannot run it.
@@ -378,7 +368,6 @@ int launch_fused(sart_engine* e, const float* x, const IterState* st) {
     a.part = e->d_part;
     a.f2part = e->d_f2part;
     a.st = st;
-    a.x_stride = a.g_stride = a.part_stride = a.f2_stride = 0;
     a.Wc = e->fu_wc;
     a.stages = e->fu_stages;
     a.stage_bytes = e->fu_stage_bytes;
@@ -522,7 +511,6 @@ int launch_solve(sart_engine* e, bool* launched) {
     a.part = e->d_part;
     a.f2part = e->d_f2part;
     a.st = nullptr;
-    a.x_stride = a.g_stride = a.part_stride = a.f2_stride = 0;
     a.Wc = e->fu_wc;
     a.stages = e->fu_stages;
     a.stage_bytes = e->fu_stage_bytes;
@@ -860,162 +848,138 @@ int run_solve(sart_engine* e, int has_guess) {
     return SART_OK;
 }
 
-// ---- two frames per sweep ---------------------------------------------------------------------------------------------
-// Frames solved without a warm start are independent right-hand sides of the same matrix, so two of them can ride on
-// one pass over it (fused_sweep_kernel<.., B = 2>: the row panel is loaded once and read twice from shared memory as
-// before, only the register slices of x and s and the FMAs double). Linear solver, one rank; everything else falls
-// back to solving the frames one after the other.
-int plan_pair(sart_engine* e) {
-    if (e->pair_planned) return SART_OK;
-    e->pair_planned = true;
-    e->pair_ok = false;
-    if (e->cfg.nranks > 1 || e->cfg.logarithmic || e->cfg.sweep_mode == SART_SWEEP_SPLIT) return SART_OK;
-    const uint32_t nt = kFusedThreads, nw = nt / 32;
-    const uint64_t max_wc = (uint64_t)nt * kFusedKMaxPair;
-    uint32_t C = 0;
-    for (uint32_t c : {1u, 2u, 4u, 8u, 16u})
-        if (ceil_div(e->ld4, c) <= max_wc) {
-            C = c;
-            break;
-        }
-    if (!C) return SART_OK;
-    const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
-    const uint32_t stage_bytes = (uint32_t)ceil_div(wc, nt) * nt * 16;
-    int max_smem = 0;
-    CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
-    uint32_t S = 0, smem = 0;
-    for (uint32_t st = 8; st >= 2; --st) {
-        const uint64_t need = (uint64_t)st * stage_bytes + (uint64_t)2 * st * 2 * nw * 4 + (uint64_t)2 * st * 2 * 16 * 4 + (uint64_t)6 * st * 8;
-        if (need + 256 <= (uint64_t)max_smem) {  // + the kernel's static shared variables
-            S = st;
-            smem = (uint32_t)need;
-            break;
-        }
-    }
-    if (!S) return SART_OK;
-    FusedKernel k = pick_fused_pair_kernel<1>((int)ceil_div(wc, nt), fused_depth(S));
-    if (!k) return SART_OK;
-    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (C > 8) CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-    cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = C;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.gridDim = dim3(C * (uint32_t)e->sm_count, 1, 1);
-    cfg.blockDim = dim3(nt + 64, 1, 1);
-    cfg.dynamicSmemBytes = smem;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    int nclusters = 0;
-    if (cudaOccupancyMaxActiveClusters(&nclusters, k, &cfg) != cudaSuccess || nclusters <= 0) {
-        (void)cudaGetLastError();
-        return SART_OK;
-    }
-    e->pr_cluster = C;
-    e->pr_wc = wc;
-    e->pr_stages = S;
-    e->pr_stage_bytes = stage_bytes;
-    e->pr_smem = smem;
-    e->pr_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
-    e->pr_kernel = k;
+// ---- several frames per matrix pass ---------------------------------------------------------------------------------------
+// Frames solved without a warm start are independent right-hand sides of the same matrix, so kGroup of them ride on
+// every pass over it (fp_rows_batch_kernel / bp_cols_batch_kernel): 2 passes per iteration for the whole group instead of
+// one fused pass per frame. Linear solver, one rank; everything else is solved frame by frame by the caller.
+constexpr int kGroup = 4;
+constexpr int kGroupFpRows = 8;
 
-    SART_TRY(dev_alloc(&e->d_pgd, 2 * e->P));
-    SART_TRY(dev_alloc(&e->d_pg, 2 * e->P));
-    SART_TRY(dev_alloc(&e->d_pxio, 2 * e->V));
-    SART_TRY(dev_alloc(&e->d_psred, 2 * (e->V + 2)));
-    SART_TRY(dev_alloc(&e->d_pf2part, 2 * (uint64_t)e->pr_nclusters));
-    SART_TRY(dev_alloc(&e->d_ppart, 2 * (uint64_t)e->pr_nclusters * e->ld));
-    SART_TRY(dev_alloc(&e->d_pfs, 2));
-    for (int k2 = 0; k2 < 2; ++k2) {
-        SART_TRY(dev_alloc(&e->d_pxd[k2], 2 * e->V));
-        SART_TRY(dev_alloc(&e->d_pxf[k2], 2 * e->ld));
-        SART_TRY(dev_alloc(&e->d_pst[k2], 2));
+int plan_group(sart_engine* e) {
+    if (e->group_planned) return SART_OK;
+    e->group_planned = true;
+    e->group_ok = false;
+    if (e->cfg.nranks > 1 || e->cfg.logarithmic) return SART_OK;
+    int fp_occ = 0, bp_occ = 0;
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, fp_rows_batch_kernel<kGroupFpRows, kFpThreads, kGroup>, kFpThreads, 0));
+    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, bp_cols_batch_kernel<kBpThreads, 8, kGroup>, kBpThreads, 0));
+    const uint64_t nrg = ceil_div(e->P, kGroupFpRows);
+    e->gp_fp_grid = (uint32_t)std::min<uint64_t>(nrg, (uint64_t)e->sm_count * std::max(fp_occ, 1));
+    // back projection: one wave of (panels x slabs) CTAs at this kernel's own occupancy, slabs a multiple of 32 rows
+    const uint64_t panels = ceil_div(e->ld4, kBpThreads);
+    uint64_t slabs = std::max<uint64_t>(1, (uint64_t)e->sm_count * std::max(bp_occ, 1) / panels);
+    slabs = std::min<uint64_t>(slabs, ceil_div(e->P, 32));
+    e->gp_bp_rows_per_slab = (uint32_t)(ceil_div(ceil_div(e->P, slabs), 32) * 32);
+    e->gp_bp_slabs = (uint32_t)ceil_div(e->P, e->gp_bp_rows_per_slab);
+
+    const uint64_t G = kGroup;
+    SART_TRY(dev_alloc(&e->d_pgd, G * e->P));
+    SART_TRY(dev_alloc(&e->d_pg, G * e->P));
+    SART_TRY(dev_alloc(&e->d_pw, G * e->P));
+    SART_TRY(dev_alloc(&e->d_pxio, G * e->V));
+    SART_TRY(dev_alloc(&e->d_psred, G * (e->V + 2)));
+    SART_TRY(dev_alloc(&e->d_pf2part, G * (uint64_t)e->gp_fp_grid));
+    SART_TRY(dev_alloc(&e->d_ppart, G * (uint64_t)e->gp_bp_slabs * e->ld));
+    SART_TRY(dev_alloc(&e->d_pfs, G));
+    for (int k = 0; k < 2; ++k) {
+        SART_TRY(dev_alloc(&e->d_pxd[k], G * e->V));
+        SART_TRY(dev_alloc(&e->d_pxf[k], G * e->ld));
+        SART_TRY(dev_alloc(&e->d_pst[k], G));
     }
-    CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_pst), 4 * sizeof(IterState)));
-    e->pair_ok = true;
+    CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_pst), 2 * G * sizeof(IterState)));
+    e->group_ok = true;
     return SART_OK;
 }
 
-// Two frames from d_pgd[0..1] to d_pxio[0..1] (device resident), default initial guess, linear solver, one rank.
-int run_solve_pair(sart_engine* e, IterState fin[2]) {
+// nf (2 .. kGroup) frames from d_pgd to d_pxio, default initial guess, no warm start. fin[f] = final state of frame f.
+int run_solve_group(sart_engine* e, int nf, IterState* fin) {
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256), pblocks = (uint32_t)ceil_div(e->P, 256);
     const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
     const uint64_t P = e->P, V = e->V, ld = e->ld;
-    // per frame: statistics, normalisation, default initial guess (one two-kernel back projection each)
-    for (int b = 0; b < 2; ++b) {
-        frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_pgd + b * P, P, e->d_pfs + b);
-        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + b * P, P, e->d_pfs + b, e->d_lambda,
-                                                             e->cfg.ray_length_threshold, e->d_pg + b * P, e->d_rinv, e->d_w,
-                                                             gpu_sem ? 2 : 1);
-        CUDA_TRY(cudaGetLastError());
-        e->launches += 2;
-        SART_TRY(backproject_weights(e));
-        start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, nullptr, e->d_rho, e->cfg.ray_density_threshold,
-                                                              e->d_pfs + b, gpu_sem ? 1.e-7 : 0.0, 0.0, 0, e->d_pxd[0] + b * V,
-                                                              e->d_pxf[0] + b * ld, V);
+    const uint64_t part_stride = (uint64_t)e->gp_bp_slabs * ld;
+
+    auto back_project = [&](const IterState* st) -> int {  // d_pw -> d_psred[f], every frame in one pass
+        BpBatchArgs b;
+        b.H = e->dH;
+        b.ld4 = e->ld4;
+        b.P = P;
+        b.w = e->d_pw;
+        b.part = e->d_ppart;
+        b.rows_per_slab = e->gp_bp_rows_per_slab;
+        b.st = st;
+        b.nframes = nf;
+        bp_cols_batch_kernel<kBpThreads, 8, kGroup>
+            <<<dim3((uint32_t)ceil_div(e->ld4, kBpThreads), e->gp_bp_slabs), kBpThreads, 0, e->stream>>>(b);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
+        for (int f = 0; f < nf; ++f) {
+            reduce_partials_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_ppart + f * part_stride, e->gp_bp_slabs, ld, V,
+                                                                   e->d_psred + f * (V + 2), st ? st + f : nullptr);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+        }
+        return SART_OK;
+    };
+
+    // per frame: statistics, normalisation, weights of the default initial guess; one pass back-projects all of them
+    for (int f = 0; f < nf; ++f) {
+        frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f);
+        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_lambda,
+                                                             e->cfg.ray_length_threshold, e->d_pg + f * P, e->d_rinv,
+                                                             e->d_pw + f * P, gpu_sem ? 2 : 1);
+        CUDA_TRY(cudaGetLastError());
+        e->launches += 2;
     }
-    init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0], e->d_pst[1]);
-    init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0] + 1, e->d_pst[1] + 1);
-    CUDA_TRY(cudaGetLastError());
-    e->launches += 2;
+    SART_TRY(back_project(nullptr));
+    for (int f = 0; f < nf; ++f) {
+        start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_psred + f * (V + 2), nullptr, e->d_rho,
+                                                              e->cfg.ray_density_threshold, e->d_pfs + f, gpu_sem ? 1.e-7 : 0.0,
+                                                              0.0, 0, e->d_pxd[0] + f * V, e->d_pxf[0] + f * ld, V);
+        init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0] + f, e->d_pst[1] + f);
+        CUDA_TRY(cudaGetLastError());
+        e->launches += 2;
+    }
     CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
 
+    // sweep t, like the two-kernel path of enqueue_sweep: projection, decision per frame, and -- unless t is the last
+    // possible sweep -- back projection, reduction and update per frame
     auto enqueue = [&](int t) -> int {
         const IterState* st_in = e->d_pst[t & 1];
         IterState* st_out = e->d_pst[(t + 1) & 1];
-        FusedArgs a;
+        const bool prof = e->profiling && t < kProfiledSweeps;
+        FpBatchArgs a;
         a.H = e->dH;
         a.ld4 = e->ld4;
         a.P = P;
         a.x = e->d_pxf[t & 1];
         a.g = e->d_pg;
         a.rinv = e->d_rinv;
-        a.part = e->d_ppart;
+        a.w = e->d_pw;
         a.f2part = e->d_pf2part;
         a.st = st_in;
-        a.x_stride = ld;
-        a.g_stride = P;
-        a.part_stride = (uint64_t)e->pr_nclusters * ld;
-        a.f2_stride = e->pr_nclusters;
-        a.Wc = e->pr_wc;
-        a.stages = e->pr_stages;
-        a.stage_bytes = e->pr_stage_bytes;
-        a.log_mode = 0;
-        cudaLaunchConfig_t cfg = {};
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = e->pr_cluster;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.gridDim = dim3(e->pr_cluster * e->pr_nclusters, 1, 1);
-        cfg.blockDim = dim3(kFusedThreads + 64, 1, 1);
-        cfg.dynamicSmemBytes = e->pr_smem;
-        cfg.stream = e->stream;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        const bool prof = e->profiling && t < kProfiledSweeps;
-        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
-        CUDA_TRY(cudaLaunchKernelEx(&cfg, e->pr_kernel, a));
-        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        a.nrg = (uint32_t)ceil_div(P, kGroupFpRows);
+        a.nframes = nf;
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
+        fp_rows_batch_kernel<kGroupFpRows, kFpThreads, kGroup><<<e->gp_fp_grid, kFpThreads, 0, e->stream>>>(a);
+        CUDA_TRY(cudaGetLastError());
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;
-        for (int b = 0; b < 2; ++b) {
-            double* sred = e->d_psred + b * (V + 2);
-            reduce_partials_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_ppart + b * a.part_stride, e->pr_nclusters, ld, V, sred,
-                                                                   st_in + b);
-            SART_TRY(launch_decide(e, t, e->d_pf2part + b * e->pr_nclusters, e->pr_nclusters, st_in + b, st_out + b, e->d_pfs + b));
-            UpdArgs u = make_update_args(e, t, st_out + b);
-            u.sred = sred;
-            u.xd_cur = e->d_pxd[t & 1] + b * V;
-            u.xd_next = e->d_pxd[(t + 1) & 1] + b * V;
-            u.xf_next = e->d_pxf[(t + 1) & 1] + b * ld;
-            u.fs = e->d_pfs + b;
+        for (int f = 0; f < nf; ++f)
+            SART_TRY(launch_decide(e, t, e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, st_in + f, st_out + f, e->d_pfs + f));
+        if (t >= e->cfg.max_iterations) return SART_OK;
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+        SART_TRY(back_project(st_out));
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        for (int f = 0; f < nf; ++f) {
+            UpdArgs u = make_update_args(e, t, st_out + f);
+            u.sred = e->d_psred + f * (V + 2);
+            u.xd_cur = e->d_pxd[t & 1] + f * V;
+            u.xd_next = e->d_pxd[(t + 1) & 1] + f * V;
+            u.xf_next = e->d_pxf[(t + 1) & 1] + f * ld;
+            u.fs = e->d_pfs + f;
             update_kernel<<<vblocks, 256, 0, e->stream>>>(u);
             CUDA_TRY(cudaGetLastError());
-            e->launches += 2;
+            ++e->launches;
         }
         return SART_OK;
     };
@@ -1028,46 +992,58 @@ int run_solve_pair(sart_engine* e, IterState fin[2]) {
             const int nb = std::min(e->batch, t_max - t + 1);
             for (int i = 0; i < nb; ++i) SART_TRY(enqueue(t + i));
             t += nb;
-            CUDA_TRY(cudaMemcpyAsync(&e->h_pst[2 * slot], e->d_pst[t & 1], 2 * sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaMemcpyAsync(&e->h_pst[kGroup * slot], e->d_pst[t & 1], nf * sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
             CUDA_TRY(cudaEventRecord(e->ev_batch[slot], e->stream));
             in_flight.push_back(slot);
             slot ^= 1;
         }
         if (in_flight.size() == 2 || t > t_max) {
-            if (in_flight.empty()) return fail(SART_ERR_STATE, "pair solve ended without a decision (internal error)");
+            if (in_flight.empty()) return fail(SART_ERR_STATE, "group solve ended without a decision (internal error)");
             const int sl = in_flight.front();
             in_flight.pop_front();
             CUDA_TRY(cudaEventSynchronize(e->ev_batch[sl]));
-            if (e->h_pst[2 * sl].done && e->h_pst[2 * sl + 1].done) {
+            bool all = true;
+            for (int f = 0; f < nf; ++f) all = all && e->h_pst[kGroup * sl + f].done;
+            if (all) {
                 done_slot = sl;
                 break;
             }
         }
     }
-    fin[0] = e->h_pst[2 * done_slot];
-    fin[1] = e->h_pst[2 * done_slot + 1];
-    for (int b = 0; b < 2; ++b) {
-        finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_pxd[0] + b * V, e->d_pxd[1] + b * V, e->d_pst[t & 1] + b,
-                                                               e->d_pfs + b, e->d_pxio + b * V, V);
+    int its = 0;
+    for (int f = 0; f < nf; ++f) {
+        fin[f] = e->h_pst[kGroup * done_slot + f];
+        its = std::max(its, fin[f].iterations);
+        finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_pxd[0] + f * V, e->d_pxd[1] + f * V, e->d_pst[t & 1] + f,
+                                                               e->d_pfs + f, e->d_pxio + f * V, V);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
     }
     float ms = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_it0, e->ev_batch[done_slot]));
     e->stats.iterate_ms = ms;
-    const int its = std::max(fin[0].iterations, fin[1].iterations);
-    e->stats.fused_ms_avg = 0;
-    e->stats.fused_launches = 0;
+    e->stats.fused_ms_avg = e->stats.tail_ms_avg = 0;
+    e->stats.fused_launches = e->stats.solve_launches = 0;
+    e->stats.fp_ms_avg = e->stats.bp_ms_avg = 0;
+    e->stats.fp_launches = e->stats.bp_launches = 0;
     if (e->profiling) {
         const int n = std::min(kProfiledSweeps, its + 1);
-        double tot = 0;
+        double fp = 0, bp = 0;
+        int nbp = 0;
         for (int k = 0; k < n; ++k) {
             float a = 0.f;
-            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][2], e->ev_prof[k][3]));
-            tot += a;
+            CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][0], e->ev_prof[k][1]));
+            fp += a;
+            if (k < its && k < e->cfg.max_iterations) {
+                CUDA_TRY(cudaEventElapsedTime(&a, e->ev_prof[k][2], e->ev_prof[k][3]));
+                bp += a;
+                ++nbp;
+            }
         }
-        e->stats.fused_ms_avg = n ? tot / n : 0;
-        e->stats.fused_launches = n;
+        e->stats.fp_ms_avg = n ? fp / n : 0;
+        e->stats.fp_launches = n;
+        e->stats.bp_ms_avg = nbp ? bp / nbp : 0;
+        e->stats.bp_launches = nbp;
     }
     return SART_OK;
 }
@@ -1244,7 +1220,7 @@ void free_engine(sart_engine* e) {
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
     void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
-                         e->d_pg, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
+                         e->d_pg, e->d_pw, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
     for (void* p : pair_ptrs)
         if (p) cudaFree(p);
     if (e->h_pst) cudaFreeHost(e->h_pst);
@@ -1694,39 +1670,39 @@ int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements
     SART_TRY(require(e, true));
     if (nframes < 0 || (nframes > 0 && (!measurements || !solutions)))
         return fail(SART_ERR_INVALID_ARGUMENT, "sart_solve_batch: NULL buffers or negative frame count");
-    SART_TRY(plan_pair(e));
+    SART_TRY(plan_group(e));
     int32_t f = 0;
     int total_launches = 0;
     double total_ms = 0;
     uint64_t h2d = 0, d2h = 0;
     while (f < nframes) {
-        if (e->pair_ok && f + 1 < nframes) {
+        const int nf = std::min<int32_t>(kGroup, nframes - f);
+        if (e->group_ok && nf >= 2) {
             e->launches = 0;
             CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
-            for (int b = 0; b < 2; ++b)
-                CUDA_TRY(cudaMemcpyAsync(e->d_pgd + b * e->P, measurements + (uint64_t)(f + b) * e->P, e->P * sizeof(double),
-                                         cudaMemcpyHostToDevice, e->stream));
-            IterState fin[2];
-            SART_TRY(run_solve_pair(e, fin));
-            for (int b = 0; b < 2; ++b)
-                CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)(f + b) * e->V, e->d_pxio + b * e->V, e->V * sizeof(double),
-                                         cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaMemcpyAsync(e->d_pgd, measurements + (uint64_t)f * e->P, (uint64_t)nf * e->P * sizeof(double),
+                                     cudaMemcpyHostToDevice, e->stream));
+            IterState fin[kGroup];
+            SART_TRY(run_solve_group(e, nf, fin));
+            CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)f * e->V, e->d_pxio, (uint64_t)nf * e->V * sizeof(double),
+                                     cudaMemcpyDeviceToHost, e->stream));
             CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
             CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
             float ms = 0.f;
             CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
             total_ms += ms;
             total_launches += e->launches;
-            h2d += 2 * e->P * sizeof(double);
-            d2h += 2 * e->V * sizeof(double);
-            for (int b = 0; b < 2; ++b) {
+            h2d += (uint64_t)nf * e->P * sizeof(double);
+            d2h += (uint64_t)nf * e->V * sizeof(double);
+            for (int b = 0; b < nf; ++b) {
                 if (status) status[f + b] = fin[b].status;
                 if (iterations) iterations[f + b] = fin[b].iterations;
             }
-            e->stats.status = fin[1].status;
-            e->stats.iterations = fin[1].iterations;
-            e->stats.sweep_mode = SART_SWEEP_FUSED;
-            f += 2;
+            e->stats.status = fin[nf - 1].status;
+            e->stats.iterations = fin[nf - 1].iterations;
+            e->stats.sweep_mode = SART_SWEEP_SPLIT;
+            e->stats.exchange_mode = SART_EXCHANGE_NONE;
+            f += nf;
         } else {
             int32_t st = 0, it = 0;
             SART_TRY(sart_solve(e, measurements + (uint64_t)f * e->P, solutions + (uint64_t)f * e->V, 0, &st, &it));

@@ -114,13 +114,12 @@ struct FusedArgs {
     const float* H;        // [P][ld]
     uint64_t ld4;          // ld / 4
     uint64_t P;
-    const float* x;        // [B][x_stride] solution(s), zero beyond nvoxel
-    const float* g;        // [B][g_stride] normalised measurement(s)
-    const float* rinv;     // [P] (shared by the frames: it depends on the matrix only)
-    float* part;           // [B][part_stride] = per frame [nclusters][ld] per-cluster partial back projection
-    double* f2part;        // [B][f2_stride]   = per frame [nclusters] per-cluster sum(fit^2)
-    const IterState* st;   // [B] or null
-    uint64_t x_stride, g_stride, part_stride, f2_stride;  // element strides between frames (unused when B == 1)
+    const float* x;        // [ld] solution, zero beyond nvoxel (the whole-solve kernel takes it from SolveArgs::xf)
+    const float* g;        // [P] normalised measurement
+    const float* rinv;     // [P] (lambda_i > h_l) ? 1 / lambda_i : 0
+    float* part;           // [nclusters][ld] per-cluster partial back projection
+    double* f2part;        // [nclusters] per-cluster sum(fit^2)
+    const IterState* st;   // may be null
     uint32_t Wc;           // float4 columns per CTA panel (last panel may be narrower)
     uint32_t stages;       // S >= 2
     uint32_t stage_bytes;  // bytes of one stage, multiple of 128
@@ -209,22 +208,18 @@ __device__ __forceinline__ bool grid_barrier(unsigned long long* ctr, unsigned l
 
 // warps 0..NWC-1 consumers, warp NWC TMA producer, warp NWC+1 reducer: 16 warps in all, so that every SM sub-partition
 // holds 4 and a thread may use 128 registers (a 17th warp caps the kernel at 96 and spills).
-// B = frames solved by the same sweep (independent right-hand sides that share the matrix: time series without warm
-// start). The matrix row is loaded once and read twice from shared memory whatever B is; only the FMAs, the register
-// slices of x and s, and the exchanged scalars are per frame.
 // D = software-pipeline depth of the consumers: FP runs D rows ahead of FIN, so the exchange latency of a row (reducer
 // wake-up, DSMEM hop, barrier) is spread over D rows of work. Requires S >= D + 1 (ring) and 2S >= S + D + 1 (slot
 // reuse, above).
-// shared memory: [S stages][2S x B x NWC warp partials][2S x B x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
+// shared memory: [S stages][2S x NWC warp partials][2S x 16 per-CTA sums][full[S], empty[S], wbar[2S], dot[2S]]
 // All ring / slot / barrier positions advance incrementally (no integer division in the row loop) and carry over
 // from one sweep of a PERSIST launch to the next.
-template <int NT, int K, int B, int D, bool PERSIST>
+template <int NT, int K, int D, bool PERSIST>
 __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* sv) {
-    static_assert(!PERSIST || B == 1, "the whole-solve kernel handles one frame");
     constexpr uint32_t NWC = NT / 32;
     constexpr uint32_t CSTRIDE = 16;  // floats per slot of per-CTA sums (cluster size <= 16), 64-byte aligned
     // 128-bit shared loads issued back to back before their FMAs (their latency overlaps); bounded by the register budget
-    constexpr int G = (B * K >= 7) ? ((B * K >= 13 || B == 1) ? 1 : 2) : (K < 4 ? K : 4);
+    constexpr int G = (K >= 7) ? 1 : (K < 4 ? K : 4);
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ int s_abort;
     __shared__ double s_f2, s_f2r[kMaxPeers];
@@ -234,11 +229,8 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
         const IterState s0 = *sv->st[0];
         if (s0.done) return;
         conv_prev = s0.conv_prev;
-    } else if (a.st) {
-        bool all_done = true;
-#pragma unroll
-        for (int b = 0; b < B; ++b) all_done = all_done && a.st[b].done;
-        if (all_done) return;
+    } else if (a.st && a.st->done) {
+        return;
     }
     const uint32_t S = a.stages;
     const uint32_t rank = cluster_ctarank(), C = cluster_nctarank();
@@ -246,9 +238,9 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     const uint32_t ring_u32 = smem_u32(smem);
-    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][B][NWC] floats
-    const uint32_t cdot_u32 = wpart_u32 + 2 * S * B * NWC * 4;       // [2S][B][CSTRIDE] floats
-    const uint32_t full_u32 = cdot_u32 + 2 * S * B * CSTRIDE * 4;
+    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][NWC] floats
+    const uint32_t cdot_u32 = wpart_u32 + 2 * S * NWC * 4;       // [2S][CSTRIDE] floats
+    const uint32_t full_u32 = cdot_u32 + 2 * S * CSTRIDE * 4;
     const uint32_t empty_u32 = full_u32 + 8 * S, wbar_u32 = empty_u32 + 8 * S, dot_u32 = wbar_u32 + 16 * S;
 
     const uint32_t c0 = rank * a.Wc;
@@ -258,7 +250,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     for (uint32_t s = 0; s < S; ++s)
         for (uint32_t o = (wcols + tid) * 16; o < a.stage_bytes; o += blockDim.x * 16)
             asm volatile("st.shared.v4.f32 [%0], {%1, %1, %1, %1};" ::"r"(ring_u32 + s * a.stage_bytes + o), "f"(0.f) : "memory");
-    for (uint32_t i = tid; i < 2 * S * B * CSTRIDE; i += blockDim.x)
+    for (uint32_t i = tid; i < 2 * S * CSTRIDE; i += blockDim.x)
         asm volatile("st.shared.f32 [%0], %1;" ::"r"(cdot_u32 + 4 * i), "f"(0.f) : "memory");
     if (tid == 0) {
         s_abort = 0;
@@ -293,7 +285,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
                 for (uint32_t r = 0; r < n; ++r) {
                     mbar_wait(empty_u32 + 8 * pr_stage, pr_parity);
-                    mbar_expect_tx(dot_u32 + 8 * pr_slot, 4 * C * B);  // one float per frame from every CTA of the cluster
+                    mbar_expect_tx(dot_u32 + 8 * pr_slot, 4 * C);  // one float from every CTA of the cluster
                     mbar_expect_tx(full_u32 + 8 * pr_stage, bytes);
                     if (bytes) bulk_load(ring_u32 + pr_stage * a.stage_bytes, src, bytes, full_u32 + 8 * pr_stage);
                     src += src_step;
@@ -312,12 +304,9 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
             for (uint32_t r = 0; r < n; ++r) {
                 mbar_wait(wbar_u32 + 8 * rd_slot, rd_parity);
-#pragma unroll
-                for (int b = 0; b < B; ++b) {
-                    float p = (lane < NWC) ? lds32(wpart_u32 + ((rd_slot * B + b) * NWC + lane) * 4) : 0.f;
-                    p = warp_sum_f32(p);  // fixed tree over the NWC partials
-                    if (lane < C) st_async_remote_f32(peer_cdot0 + (rd_slot * B + b) * (CSTRIDE * 4), p, peer_dot0 + 8 * rd_slot);
-                }
+                float p = (lane < NWC) ? lds32(wpart_u32 + (rd_slot * NWC + lane) * 4) : 0.f;
+                p = warp_sum_f32(p);  // fixed tree over the NWC partials
+                if (lane < C) st_async_remote_f32(peer_cdot0 + rd_slot * (CSTRIDE * 4), p, peer_dot0 + 8 * rd_slot);
                 if (++rd_slot == 2 * S) {
                     rd_slot = 0;
                     rd_parity ^= 1;
@@ -327,31 +316,25 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
         } else {
             // ---- consumers -------------------------------------------------------------------------------------------
             const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
-            float4 xr[B][K], sacc[B][K];
+            float4 xr[K], sacc[K];
+            const float4* x4 = reinterpret_cast<const float4*>(xcur) + c0 + tid;
 #pragma unroll
-            for (int b = 0; b < B; ++b) {
-                const float4* x4 = reinterpret_cast<const float4*>(xcur + b * a.x_stride) + c0 + tid;
-#pragma unroll
-                for (int m = 0; m < K; ++m) {
-                    // a PERSIST launch reads what the previous tail wrote: through L2, never the read-only path
-                    xr[b][m] = (m < mine) ? (PERSIST ? __ldcg(x4 + m * NT) : __ldg(x4 + m * NT)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                    sacc[b][m] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
+            for (int m = 0; m < K; ++m) {
+                // a PERSIST launch reads what the previous tail wrote: through L2, never the read-only path
+                xr[m] = (m < mine) ? (PERSIST ? __ldcg(x4 + m * NT) : __ldg(x4 + m * NT)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                sacc[m] = make_float4(0.f, 0.f, 0.f, 0.f);
             }
-            double f2acc[B];
-#pragma unroll
-            for (int b = 0; b < B; ++b) f2acc[b] = 0.0;
+            double f2acc = 0.0;
             // Measurements and inverse ray lengths of the cluster's rows are fetched 32 rows at a time: lane l holds row
             // 32j + l of batch j, the batch after the current one is already in flight, and each row's values are
             // broadcast with a shuffle. A per-row load, however early it is issued, ends up waited for within the row
             // (its register is touched when the pipeline queue shifts), which put one exposed L2/HBM latency on every
             // row and capped short rows at ~0.75 us each.
-            float g_cur[B], g_nxt[B], r_cur = 0.f, r_nxt = 0.f;
+            float g_cur = 0.f, g_nxt = 0.f, r_cur = 0.f, r_nxt = 0.f;
             auto load_batch = [&](uint32_t t0) {
                 const uint32_t row = t0 + lane;
                 const uint64_t off = (uint64_t)cid + (uint64_t)row * ncl;
-#pragma unroll
-                for (int b = 0; b < B; ++b) g_nxt[b] = (row < n) ? __ldg(a.g + b * a.g_stride + off) : 0.f;
+                g_nxt = (row < n) ? __ldg(a.g + off) : 0.f;
                 r_nxt = (row < n) ? __ldg(a.rinv + off) : 0.f;
             };
             const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
@@ -359,9 +342,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             auto forward = [&]() {
                 mbar_wait(full_u32 + 8 * fp_stage, fp_parity);
                 const uint32_t base = ring_u32 + fp_stage * a.stage_bytes + tid * 16;
-                float acc[B][4];
-#pragma unroll
-                for (int b = 0; b < B; ++b) acc[b][0] = acc[b][1] = acc[b][2] = acc[b][3] = 0.f;
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
                 for (int m0 = 0; m0 < K; m0 += G) {
                     float4 h[G];
@@ -371,22 +352,15 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
 #pragma unroll
                     for (int j = 0; j < G; ++j)
                         if (m0 + j < K) {
-#pragma unroll
-                            for (int b = 0; b < B; ++b) {
-                                acc[b][0] = fmaf(h[j].x, xr[b][m0 + j].x, acc[b][0]);
-                                acc[b][1] = fmaf(h[j].y, xr[b][m0 + j].y, acc[b][1]);
-                                acc[b][2] = fmaf(h[j].z, xr[b][m0 + j].z, acc[b][2]);
-                                acc[b][3] = fmaf(h[j].w, xr[b][m0 + j].w, acc[b][3]);
-                            }
+                            acc[0] = fmaf(h[j].x, xr[m0 + j].x, acc[0]);
+                            acc[1] = fmaf(h[j].y, xr[m0 + j].y, acc[1]);
+                            acc[2] = fmaf(h[j].z, xr[m0 + j].z, acc[2]);
+                            acc[3] = fmaf(h[j].w, xr[m0 + j].w, acc[3]);
                         }
                 }
-                float tot[B];
-#pragma unroll
-                for (int b = 0; b < B; ++b) tot[b] = warp_sum_f32((acc[b][0] + acc[b][1]) + (acc[b][2] + acc[b][3]));
+                const float tot = warp_sum_f32((acc[0] + acc[1]) + (acc[2] + acc[3]));
                 if (lane == 0) {
-#pragma unroll
-                    for (int b = 0; b < B; ++b)
-                        asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + ((fp_slot * B + b) * NWC + warp) * 4), "f"(tot[b]) : "memory");
+                    asm volatile("st.shared.f32 [%0], %1;" ::"r"(wpart_u32 + (fp_slot * NWC + warp) * 4), "f"(tot) : "memory");
                     mbar_arrive(wbar_u32 + 8 * fp_slot);  // release: the reducer sees the partials
                 }
                 if (++fp_stage == S) {
@@ -396,22 +370,18 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 if (++fp_slot == 2 * S) fp_slot = 0;
             };
 
-            auto finish = [&](const float (&gi)[B], float ri) {
+            auto finish = [&](float gi, float ri) {
                 mbar_wait(dot_u32 + 8 * fin_slot, fin_parity);
-                float wi[B];
-#pragma unroll
-                for (int b = 0; b < B; ++b) {
-                    // the C per-CTA sums in rank order: the same additions in every thread of the cluster
-                    float fitv = 0.f;
-                    const uint32_t cd = cdot_u32 + (fin_slot * B + b) * (CSTRIDE * 4);
-                    for (uint32_t q = 0; q < c4; ++q) {  // slots of ranks >= C hold zeros
-                        const float4 v = lds128(cd + q * 16);
-                        fitv = (((fitv + v.x) + v.y) + v.z) + v.w;
-                    }
-                    wi[b] = 0.f;
-                    if (gi[b] >= 0.f) wi[b] = a.log_mode ? fitv * ri : (gi[b] - fitv) * ri;
-                    f2acc[b] += (double)fitv * (double)fitv;
+                // the C per-CTA sums in rank order: the same additions in every thread of the cluster
+                float fitv = 0.f;
+                const uint32_t cd = cdot_u32 + fin_slot * (CSTRIDE * 4);
+                for (uint32_t q = 0; q < c4; ++q) {  // slots of ranks >= C hold zeros
+                    const float4 v = lds128(cd + q * 16);
+                    fitv = (((fitv + v.x) + v.y) + v.z) + v.w;
                 }
+                float wi = 0.f;
+                if (gi >= 0.f) wi = a.log_mode ? fitv * ri : (gi - fitv) * ri;
+                f2acc += (double)fitv * (double)fitv;
                 const uint32_t base = ring_u32 + fin_stage * a.stage_bytes + tid * 16;
 #pragma unroll
                 for (int m0 = 0; m0 < K; m0 += G) {
@@ -422,13 +392,10 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
 #pragma unroll
                     for (int j = 0; j < G; ++j)
                         if (m0 + j < K) {
-#pragma unroll
-                            for (int b = 0; b < B; ++b) {
-                                sacc[b][m0 + j].x = fmaf(h[j].x, wi[b], sacc[b][m0 + j].x);
-                                sacc[b][m0 + j].y = fmaf(h[j].y, wi[b], sacc[b][m0 + j].y);
-                                sacc[b][m0 + j].z = fmaf(h[j].z, wi[b], sacc[b][m0 + j].z);
-                                sacc[b][m0 + j].w = fmaf(h[j].w, wi[b], sacc[b][m0 + j].w);
-                            }
+                            sacc[m0 + j].x = fmaf(h[j].x, wi, sacc[m0 + j].x);
+                            sacc[m0 + j].y = fmaf(h[j].y, wi, sacc[m0 + j].y);
+                            sacc[m0 + j].z = fmaf(h[j].z, wi, sacc[m0 + j].z);
+                            sacc[m0 + j].w = fmaf(h[j].w, wi, sacc[m0 + j].w);
                         }
                 }
                 __syncwarp();
@@ -448,26 +415,20 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             for (uint32_t r = 0; r < n; ++r) {
                 if ((r & 31) == 0) {
                     r_cur = r_nxt;
-#pragma unroll
-                    for (int b = 0; b < B; ++b) g_cur[b] = g_nxt[b];
+                    g_cur = g_nxt;
                     load_batch(r + 32);
                 }
-                float gi[B];
-#pragma unroll
-                for (int b = 0; b < B; ++b) gi[b] = __shfl_sync(FULL_MASK, g_cur[b], r & 31);
+                const float gi = __shfl_sync(FULL_MASK, g_cur, r & 31);
                 const float ri = __shfl_sync(FULL_MASK, r_cur, r & 31);
                 if (r + D < n) forward();
                 finish(gi, ri);
             }
 
+            float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part) + (uint64_t)cid * a.ld4 + c0 + tid;
 #pragma unroll
-            for (int b = 0; b < B; ++b) {
-                float4* __restrict__ out4 = reinterpret_cast<float4*>(a.part + b * a.part_stride) + (uint64_t)cid * a.ld4 + c0 + tid;
-#pragma unroll
-                for (int m = 0; m < K; ++m)
-                    if (m < mine) out4[m * NT] = sacc[b][m];
-                if (rank == 0 && tid == 0) a.f2part[b * a.f2_stride + cid] = f2acc[b];
-            }
+            for (int m = 0; m < K; ++m)
+                if (m < mine) out4[m * NT] = sacc[m];
+            if (rank == 0 && tid == 0) a.f2part[cid] = f2acc;
         }
         if constexpr (!PERSIST) {
             break;
@@ -603,15 +564,15 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     cluster_sync_all();
 }
 
-template <int NT, int K, int B, int D>
+template <int NT, int K, int D>
 __global__ void __launch_bounds__(NT + 64, 1) fused_sweep_kernel(const FusedArgs a) {
-    fused_body<NT, K, B, D, false>(a, nullptr);
+    fused_body<NT, K, D, false>(a, nullptr);
 }
 
 // the whole solve: sweeps 0 .. stop in one cooperative launch (one frame)
 template <int NT, int K, int D>
 __global__ void __launch_bounds__(NT + 64, 1) fused_solve_kernel(const FusedArgs a, const SolveArgs sv) {
-    fused_body<NT, K, 1, D, true>(a, &sv);
+    fused_body<NT, K, D, true>(a, &sv);
 }
 
 }  // namespace sart

@@ -251,6 +251,171 @@ __global__ void __launch_bounds__(NT) bp_cols_kernel(const BpArgs a) {
     bp_cols_body<NT, U>(a, a.part);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// F independent frames per pass over the matrix (sart_solve_batch). Frames solved without a warm start
+// share nothing but H, so one sweep can serve F of them: the forward projection becomes [P x V] x [V x F], the back
+// projection [V x P] x [P x F] -- still CUDA-core fp32 (TF32 tensor cores would lose the 1e-5 parity) and still
+// HBM-bound at F = 4: 4 FMAs per matrix element against 0.5 flop/byte of headroom. Same thread mappings, summation
+// orders and epilogues as the single-frame kernels above, with an extra frame index on x, g, w, the partials and the
+// control blocks. A frame that is done keeps being multiplied (its results are ignored): the pass costs the same.
+// ---------------------------------------------------------------------------------------------------------------------
+struct FpBatchArgs {
+    const float* H;
+    uint64_t ld4, P;
+    const float* x;       // [F][ld]
+    const float* g;       // [F][P]
+    const float* rinv;    // [P]
+    float* w;             // [F][P]
+    double* f2part;       // [F][gridDim.x]
+    const IterState* st;  // [F] or null
+    uint32_t nrg;
+    int nframes;          // frames in use (<= F); the others are skipped in the epilogue
+};
+
+template <int R, int NT, int F>
+__global__ void __launch_bounds__(NT, 2) fp_rows_batch_kernel(const FpBatchArgs a) {
+    if (a.st) {
+        bool all_done = true;
+        for (int f = 0; f < a.nframes; ++f) all_done = all_done && a.st[f].done;
+        if (all_done) return;
+    }
+    constexpr int NW = NT / 32;
+    __shared__ double red[R][F][NW];
+    __shared__ double f2s[R][F];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float4* __restrict__ H4 = reinterpret_cast<const float4*>(a.H);
+    const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x);
+    const uint32_t ld4 = (uint32_t)a.ld4;
+    double f2acc = 0.0;  // thread (r, f) = tid: row slot r of frame f
+
+    for (uint32_t rg = blockIdx.x; rg < a.nrg; rg += gridDim.x) {
+        const uint64_t row0 = (uint64_t)rg * R;
+        const int nvalid = (int)min((uint64_t)R, a.P - row0);
+        const float4* __restrict__ base = H4 + row0 * a.ld4;
+        uint32_t roff[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) roff[r] = (r < nvalid ? r : 0) * ld4;
+
+        float acc[R][F];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int f = 0; f < F; ++f) acc[r][f] = 0.f;
+
+        for (uint32_t c = tid; c < ld4; c += NT) {
+            float4 xv[F], h[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) h[r] = ldg_stream(base + roff[r] + c);
+#pragma unroll
+            for (int f = 0; f < F; ++f) xv[f] = __ldg(x4 + (uint64_t)f * ld4 + c);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    acc[r][f] = fmaf(h[r].x, xv[f].x, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].y, xv[f].y, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].z, xv[f].z, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].w, xv[f].w, acc[r][f]);
+                }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int f = 0; f < F; ++f) {
+                const double s = warp_sum((double)acc[r][f]);
+                if (lane == 0) red[r][f][warp] = s;
+            }
+        __syncthreads();
+        if (tid < R * F) {
+            const int r = tid / F, f = tid % F;
+            if (r < nvalid && f < a.nframes) {
+                double s = 0.0;
+#pragma unroll
+                for (int k = 0; k < NW; ++k) s += red[r][f][k];
+                const uint64_t i = row0 + r;
+                const float fitv = (float)s;
+                f2acc += s * s;
+                const float gi = a.g[(uint64_t)f * a.P + i];
+                a.w[(uint64_t)f * a.P + i] = (gi >= 0.f) ? (gi - fitv) * a.rinv[i] : 0.f;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid < R * F) f2s[tid / F][tid % F] = f2acc;
+    __syncthreads();
+    if (tid < a.nframes) {
+        double s = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) s += f2s[r][tid];
+        a.f2part[(uint64_t)tid * gridDim.x + blockIdx.x] = s;
+    }
+}
+
+struct BpBatchArgs {
+    const float* H;
+    uint64_t ld4, P;
+    const float* w;   // [F][P]
+    float* part;      // [F][nslabs][ld]
+    uint32_t rows_per_slab;
+    const IterState* st;  // [F] or null
+    int nframes;
+};
+
+template <int NT, int U, int F>
+__global__ void __launch_bounds__(NT) bp_cols_batch_kernel(const BpBatchArgs a) {
+    if (a.st) {
+        bool all_done = true;
+        for (int f = 0; f < a.nframes; ++f) all_done = all_done && a.st[f].done;
+        if (all_done) return;
+    }
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint64_t c4 = (uint64_t)blockIdx.x * NT + tid;
+    const bool active = c4 < a.ld4;
+    const float4* __restrict__ base = reinterpret_cast<const float4*>(a.H) + (active ? c4 : a.ld4 - 1);
+    const uint64_t r0 = (uint64_t)blockIdx.y * a.rows_per_slab;
+    const uint64_t r1 = min(a.P, r0 + a.rows_per_slab);
+
+    float4 acc[F];
+#pragma unroll
+    for (int f = 0; f < F; ++f) acc[f] = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto fma_row = [&](const float4& h, const float (&wl)[F], int src_lane) {
+#pragma unroll
+        for (int f = 0; f < F; ++f) {
+            const float wv = __shfl_sync(FULL_MASK, wl[f], src_lane);
+            acc[f].x = fmaf(h.x, wv, acc[f].x);
+            acc[f].y = fmaf(h.y, wv, acc[f].y);
+            acc[f].z = fmaf(h.z, wv, acc[f].z);
+            acc[f].w = fmaf(h.w, wv, acc[f].w);
+        }
+    };
+    for (uint64_t r = r0; r < r1; r += 32) {
+        const uint64_t rl = r + lane;
+        float wl[F];
+#pragma unroll
+        for (int f = 0; f < F; ++f) wl[f] = (rl < r1 && f < a.nframes) ? __ldg(a.w + (uint64_t)f * a.P + rl) : 0.f;
+        const float4* __restrict__ p = base + r * a.ld4;
+        if (r + 32 <= r1) {
+#pragma unroll
+            for (int k = 0; k < 32; k += U) {
+                float4 h[U];  // U unconditional 128-bit loads in flight before the first FMA
+#pragma unroll
+                for (int u = 0; u < U; ++u) h[u] = ldg_stream(p + (uint64_t)(k + u) * a.ld4);
+#pragma unroll
+                for (int u = 0; u < U; ++u) fma_row(h[u], wl, k + u);
+            }
+        } else {
+            const int n = (int)(r1 - r);
+            for (int k = 0; k < n; ++k) fma_row(ldg_stream(p + (uint64_t)k * a.ld4), wl, k);
+        }
+    }
+    if (active) {
+        const uint64_t nslabs = gridDim.y;
+#pragma unroll
+        for (int f = 0; f < F; ++f)
+            if (f < a.nframes) reinterpret_cast<float4*>(a.part)[((uint64_t)f * nslabs + blockIdx.y) * a.ld4 + c4] = acc[f];
+    }
+}
+
 // s_j = sum over slabs (fixed order, fp64) -> sred[j]
 // When f2part is given, warp 0 of block 0 also adds the nf2 partials of sum(fit^2) into sred[V] (one launch less
 // where the scalar travels with the vector).

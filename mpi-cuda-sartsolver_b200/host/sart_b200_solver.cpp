@@ -237,7 +237,7 @@ int main(int argc, char* argv[]) {
     std::vector<int32_t> all_status, all_iterations;
 
     // source/main.cpp:127-140. With --no_guess consecutive frames do not depend on each other, so they are handed to the
-    // engine two at a time (sart_solve_batch: one pass over the matrix per iteration serves both).
+    // engine four at a time (sart_solve_batch: every pass over the matrix serves the whole group).
     auto store = [&](size_t k, const double* x, int32_t status, int32_t iterations) {
         const double t = frames->frame_time(k);
         if (rank != 0) return;  // source/main.cpp:134: only the root stores solutions
@@ -268,20 +268,20 @@ int main(int argc, char* argv[]) {
     std::vector<double> solution_vec, frame;
     size_t k = 0;
     while (k < frames->size()) {
-        const size_t nb = (config.no_guess && k + 1 < frames->size()) ? 2 : 1;
-        if (nb == 2) {
-            std::vector<double> pair_frames(2 * npixel_local), pair_solutions(2 * nvoxel), one;
-            for (size_t b = 0; b < 2; ++b) {
+        const size_t nb = config.no_guess ? std::min<size_t>(4, frames->size() - k) : 1;
+        if (nb >= 2) {
+            std::vector<double> group_frames(nb * npixel_local), group_solutions(nb * nvoxel), one;
+            for (size_t b = 0; b < nb; ++b) {
                 if (!frames->read(k + b, offset_pixel, npixel_local, one, error)) die(error);
-                std::copy(one.begin(), one.end(), pair_frames.begin() + b * npixel_local);
+                std::copy(one.begin(), one.end(), group_frames.begin() + b * npixel_local);
             }
             const auto last = std::chrono::steady_clock::now();
-            int32_t status[2] = {0, 0}, iterations[2] = {0, 0};
-            must(sart_solve_batch(engine, 2, pair_frames.data(), pair_solutions.data(), status, iterations));
+            std::vector<int32_t> status(nb, 0), iterations(nb, 0);
+            must(sart_solve_batch(engine, (int32_t)nb, group_frames.data(), group_solutions.data(), status.data(), iterations.data()));
             const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
-            for (size_t b = 0; b < 2; ++b) {
-                if (rank == 0) std::cout << "Processed in: " << duration.count() / 2 << " ms" << std::endl;
-                store(k + b, pair_solutions.data() + b * nvoxel, status[b], iterations[b]);
+            for (size_t b = 0; b < nb; ++b) {
+                if (rank == 0) std::cout << "Processed in: " << duration.count() / (double)nb << " ms" << std::endl;
+                store(k + b, group_solutions.data() + b * nvoxel, status[b], iterations[b]);
                 flush(k + b + 1);
             }
         } else {

@@ -485,11 +485,13 @@ def test_randomised_problems_against_the_oracle(seed, sart, restatement):
 
 @pytest.mark.parametrize("P,V,tol", [(700, 1000, None), (512, 50000, None), (300, 20000, 1e-4), (257, 77, 1e-4)])
 def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, sart, restatement):
-    """sart_solve_batch (two frames per matrix sweep) against solving every frame on its own and against the oracle: five
-    frames, so two pairs and one single; frames of one pair converge at different iterations when the tolerance decides."""
+    """sart_solve_batch (four frames per matrix pass) against solving every frame on its own and against the oracle: seven
+    frames, so one full group and one of three; frames of a group converge at different iterations when the tolerance
+    decides."""
     syn = load_synthetic()
     H = restatement.fill_synthetic(P, V, 321)
-    frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=t) * (1.0 + 3.0 * t)) for t in (0.0, 0.3, 0.55, 0.8, 1.0)])
+    times = (0.0, 0.3, 0.55, 0.8, 1.0, 0.15, 0.65)
+    frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=t) * (1.0 + 3.0 * t)) for t in times])
     frames[1, ::19] = -1.0
     lap = syn.laplacian_coo(V)
     kw = dict(beta_laplace=2e-2, max_iterations=9, fixed_iterations=True) if tol is None else \
@@ -500,7 +502,7 @@ def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, sart, res
         eng.finalize()
         xb, stb, itb = eng.solve_batch(frames)
         singles = [eng.solve(f) for f in frames]
-    for f in range(5):
+    for f in range(len(times)):
         xs, sts, its = singles[f]
         assert abs(int(itb[f]) - its) <= 1
         if itb[f] == its:

@@ -5,7 +5,7 @@ echo "== batch on c2 =="
 timeout 300 python tools/run_config.py --config c2 --batch 8 --iterations 10 2>&1 | grep CONFIG | python -c "
 import sys, json
 for l in sys.stdin:
-    d = json.loads(l[7:]); print({k: d[k] for k in ('speedup','pair_sweep_ms','single_sweep_ms','frame_iterations_per_s_batch','frame_iterations_per_s_one_by_one','max_rel_l2_batch_vs_single')})"
+    d = json.loads(l[7:]); print({k: d[k] for k in ('speedup','group_iteration_ms','group_fp_ms','group_bp_ms','single_sweep_ms','frame_iterations_per_s_batch','frame_iterations_per_s_one_by_one','max_rel_l2_batch_vs_single')})"
 echo "== short rows: depth 1 vs 3 =="
 for V in 4096 8192 16384; do
   P=$((2000000000 / V))

@@ -73,11 +73,12 @@ def main():
     if args.batch:
         F = args.batch
         frames = np.stack([eng.forward_project(syn.emission_profile(V, t=f / max(1, F - 1))) for f in range(F)])
-        eng.solve_batch(frames[:2])  # warm-up (allocates the pair buffers)
+        eng.solve_batch(frames[:2])  # warm-up (allocates the group buffers)
         t1 = time.perf_counter()
         xb, stb, itb = eng.solve_batch(frames)
         t_batch = time.perf_counter() - t1
-        pair_ms = eng.stats().fused_ms_avg
+        sb = eng.stats()
+        pair_ms = sb.fp_ms_avg + sb.bp_ms_avg  # one batched forward + one batched back projection = an iteration of 4 frames
         t1 = time.perf_counter()
         singles = [eng.solve(f) for f in frames]
         t_single = time.perf_counter() - t1
@@ -86,7 +87,8 @@ def main():
         out.update({"batch_frames": F, "iterations_per_frame": int(itb[0]), "batch_s": t_batch, "one_by_one_s": t_single,
                     "frame_iterations_per_s_batch": float(np.sum(itb)) / t_batch,
                     "frame_iterations_per_s_one_by_one": float(sum(s[2] for s in singles)) / t_single,
-                    "speedup": t_single / t_batch, "pair_sweep_ms": pair_ms, "single_sweep_ms": single_ms,
+                    "speedup": t_single / t_batch, "group_iteration_ms": pair_ms, "group_fp_ms": sb.fp_ms_avg,
+                    "group_bp_ms": sb.bp_ms_avg, "single_sweep_ms": single_ms,
                     "max_rel_l2_batch_vs_single": worst, "x_checksum": float(np.dot(xb[-1], np.arange(1, V + 1)))})
     elif not series:
         xs = syn.emission_profile(V)
