@@ -119,6 +119,7 @@ struct sart_engine {
     // whole solve in one cooperative launch (fused_solve_kernel); falls back to one launch per sweep when unavailable
     bool persistent = false;
     void (*fs_kernel)(const sart::FusedArgs, const sart::SolveArgs) = nullptr;
+    uint32_t fs_nclusters = 0;
     unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer
     uint64_t xchg_cta_flag_off = 0;             // per-CTA flags of the in-kernel exchange inside a region
 
@@ -338,22 +339,24 @@ int plan_fused(sart_engine* e) {
     e->fu_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
     e->fused = true;
 
-    // whole solve in one cooperative launch, when the device can co-schedule the same grid for that kernel
+    // Whole solve in one cooperative launch (fused_solve_kernel), when the device can co-schedule its grid. Its tail needs
+    // more registers than the bare sweep, so on narrow panels fewer of its CTAs fit an SM; both kernels then run the
+    // smaller grid, which keeps the two ways of running a solve bit-identical (same clusters, same partial sums).
     e->persistent = false;
     int coop = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, e->device));
-    if (coop && env_int("SART_PERSISTENT", 1) != 0) {
-        const SolveKernel sk = pick_solve_kernel<1>(k_need, fused_depth(S));
-        int ncl2 = 0;
-        if (sk && cudaFuncSetAttribute(sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
-            (C <= 8 || cudaFuncSetAttribute(sk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
-            cudaOccupancyMaxActiveClusters(&ncl2, sk, &cfg) == cudaSuccess && ncl2 >= (int)e->fu_nclusters) {
-            e->fs_kernel = sk;
-            e->persistent = true;
-            if (!e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 4));
-        }
-        (void)cudaGetLastError();
+    const SolveKernel sk = pick_solve_kernel<1>(k_need, fused_depth(S));
+    int ncl2 = 0;
+    if (sk && cudaFuncSetAttribute(sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
+        (C <= 8 || cudaFuncSetAttribute(sk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
+        cudaOccupancyMaxActiveClusters(&ncl2, sk, &cfg) == cudaSuccess && ncl2 > 0) {
+        e->fu_nclusters = std::min(e->fu_nclusters, (uint32_t)ncl2);
+        e->fs_kernel = sk;
+        e->fs_nclusters = e->fu_nclusters;
+        e->persistent = coop && env_int("SART_PERSISTENT", 1) != 0;
+        if (e->persistent && !e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 4));
     }
+    (void)cudaGetLastError();
     return SART_OK;
 }
 
@@ -546,7 +549,7 @@ int launch_solve(sart_engine* e, bool* launched) {
     attr[0].val.clusterDim.z = 1;
     attr[1].id = cudaLaunchAttributeCooperative;
     attr[1].val.cooperative = 1;
-    cfg.gridDim = dim3(e->fu_cluster * e->fu_nclusters, 1, 1);
+    cfg.gridDim = dim3(e->fu_cluster * e->fs_nclusters, 1, 1);
     cfg.blockDim = dim3(e->fu_threads, 1, 1);
     cfg.dynamicSmemBytes = e->fu_smem;
     cfg.stream = e->stream;
@@ -1135,7 +1138,7 @@ int setup_peer_exchange(sart_engine* e) {
     int ok = !(mode && std::string(mode) == "nccl") && e->cfg.nranks <= kMaxPeers;
     // [one flag per rank, 128 B apart][one flag per rank and CTA of the whole-solve kernel][buffer 0][buffer 1]
     // a buffer holds V + 1 doubles (per-sweep kernels) or one record [sum(fit^2)][chunk] per CTA (whole-solve kernel)
-    const uint64_t nblk = std::max<uint64_t>((uint64_t)e->fu_cluster * e->fu_nclusters, 1);
+    const uint64_t nblk = std::max<uint64_t>((uint64_t)e->fu_cluster * (e->persistent ? e->fs_nclusters : e->fu_nclusters), 1);
     const uint64_t rank_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
     const uint64_t flags_bytes = rank_flags_bytes + ceil_div((uint64_t)e->cfg.nranks * nblk * 8, 256) * 256;
     const uint64_t buf_bytes = ceil_div((e->V + 2 * nblk + 2) * sizeof(double), 256) * 256;

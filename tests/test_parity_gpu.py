@@ -134,7 +134,8 @@ def test_fixed_iterations_parity_across_shapes(P, V, iters, mode, sart, restatem
         assert s.gpu_launches >= 4 * iters
 
 
-@pytest.mark.parametrize("P,V,log,tol", [(3000, 4100, 0, 1e-5), (700, 20000, 0, 1e-30), (1500, 9000, 1, 1e-5), (64, 5000, 0, 1e-4)])
+@pytest.mark.parametrize("P,V,log,tol", [(3000, 4100, 0, 1e-5), (700, 20000, 0, 1e-30), (1500, 9000, 1, 1e-5), (64, 5000, 0, 1e-4),
+                                         (1536, 640, 0, 1e-30), (5000, 2000, 0, 1e-5)])
 def test_whole_solve_kernel_is_bit_identical_to_one_launch_per_sweep(P, V, log, tol, sart, restatement, monkeypatch):
     """fused_solve_kernel (all sweeps, cluster reduction, decision and update inside one cooperative launch) repeats the
     arithmetic of the per-sweep kernels in the same order: same bits, same status, same stopping iteration."""
