@@ -192,7 +192,7 @@ int sart_solve(sart_engine* e, const double* measurement, double* solution, int3
  * with solution_vec.clear() after every frame -- in one call. Such frames are independent right-hand sides of the same
  * matrix, so the engine solves them four at a time: every pass over the matrix (forward projection, back projection)
  * serves the whole group, 2 passes per iteration for four frames instead of one fused pass per frame (linear solver,
- * one rank; otherwise, and for a last single frame, the frames are solved one after the other, same results).
+ * any number of ranks; the log solver and a last single frame are solved one after the other, same results). COLLECTIVE.
  *   measurements [nframes][nrows], solutions [nframes][nvoxel] (host, double); status, iterations [nframes] or NULL.
  * Every frame gets exactly what sart_solve(has_guess = 0) would give it, within the parity tolerance. */
 int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements, double* solutions, int32_t* status,

@@ -139,7 +139,7 @@ struct sart_engine {
     // several frames per matrix pass (sart_solve_batch): geometry + buffers for kGroup frames, allocated on first use
     bool group_planned = false, group_ok = false;
     uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
-    double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr;
+    double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr;
     double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
     float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
     float *d_pg = nullptr, *d_pw = nullptr, *d_ppart = nullptr;
@@ -854,7 +854,8 @@ int run_solve(sart_engine* e, int has_guess) {
 // ---- several frames per matrix pass ---------------------------------------------------------------------------------------
 // Frames solved without a warm start are independent right-hand sides of the same matrix, so kGroup of them ride on
 // every pass over it (fp_rows_batch_kernel / bp_cols_batch_kernel): 2 passes per iteration for the whole group instead of
-// one fused pass per frame. Linear solver, one rank; everything else is solved frame by frame by the caller.
+// one fused pass per frame. Linear solver; with several ranks the per-frame sums travel in one NCCL all-reduce per
+// pass. The log solver and a last single frame are solved frame by frame by the caller.
 constexpr int kGroup = 4;
 constexpr int kGroupFpRows = 8;
 
@@ -862,7 +863,7 @@ int plan_group(sart_engine* e) {
     if (e->group_planned) return SART_OK;
     e->group_planned = true;
     e->group_ok = false;
-    if (e->cfg.nranks > 1 || e->cfg.logarithmic) return SART_OK;
+    if (e->cfg.logarithmic) return SART_OK;
     int fp_occ = 0, bp_occ = 0;
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, fp_rows_batch_kernel<kGroupFpRows, kFpThreads, kGroup>, kFpThreads, 0));
     CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, bp_cols_batch_kernel<kBpThreads, 8, kGroup>, kBpThreads, 0));
@@ -882,6 +883,7 @@ int plan_group(sart_engine* e) {
     SART_TRY(dev_alloc(&e->d_pxio, G * e->V));
     SART_TRY(dev_alloc(&e->d_psred, G * (e->V + 2)));
     SART_TRY(dev_alloc(&e->d_pf2part, G * (uint64_t)e->gp_fp_grid));
+    SART_TRY(dev_alloc(&e->d_pf2sum, G));
     SART_TRY(dev_alloc(&e->d_ppart, G * (uint64_t)e->gp_bp_slabs * e->ld));
     SART_TRY(dev_alloc(&e->d_pfs, G));
     for (int k = 0; k < 2; ++k) {
@@ -921,12 +923,14 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
             CUDA_TRY(cudaGetLastError());
             ++e->launches;
         }
-        return SART_OK;
+        return allreduce_f64(e, e->d_psred, (uint64_t)nf * (V + 2), ncclSum);  // over the row shards, all frames at once
     };
 
     // per frame: statistics, normalisation, weights of the default initial guess; one pass back-projects all of them
     for (int f = 0; f < nf; ++f) {
         frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f);
+        SART_TRY(allreduce_f64(e, &e->d_pfs[f].gmax, 1, ncclMax));
+        SART_TRY(allreduce_f64(e, &e->d_pfs[f].gsq, 1, ncclSum));
         frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_lambda,
                                                              e->cfg.ray_length_threshold, e->d_pg + f * P, e->d_rinv,
                                                              e->d_pw + f * P, gpu_sem ? 2 : 1);
@@ -967,8 +971,18 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         CUDA_TRY(cudaGetLastError());
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;
-        for (int f = 0; f < nf; ++f)
-            SART_TRY(launch_decide(e, t, e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, st_in + f, st_out + f, e->d_pfs + f));
+        if (e->cfg.nranks > 1) {  // sum(fit^2) of every frame over the row shards before the decisions
+            for (int f = 0; f < nf; ++f) {
+                f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, e->d_pf2sum + f, st_in + f);
+                CUDA_TRY(cudaGetLastError());
+                ++e->launches;
+            }
+            SART_TRY(allreduce_f64(e, e->d_pf2sum, (uint64_t)nf, ncclSum));
+            for (int f = 0; f < nf; ++f) SART_TRY(launch_decide(e, t, e->d_pf2sum + f, 1, st_in + f, st_out + f, e->d_pfs + f));
+        } else {
+            for (int f = 0; f < nf; ++f)
+                SART_TRY(launch_decide(e, t, e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, st_in + f, st_out + f, e->d_pfs + f));
+        }
         if (t >= e->cfg.max_iterations) return SART_OK;
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
         SART_TRY(back_project(st_out));
@@ -1222,7 +1236,7 @@ void free_engine(sart_engine* e) {
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
-    void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
+    void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
                          e->d_pg, e->d_pw, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
     for (void* p : pair_ptrs)
         if (p) cudaFree(p);
@@ -1704,7 +1718,7 @@ int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements
             e->stats.status = fin[nf - 1].status;
             e->stats.iterations = fin[nf - 1].iterations;
             e->stats.sweep_mode = SART_SWEEP_SPLIT;
-            e->stats.exchange_mode = SART_EXCHANGE_NONE;
+            e->stats.exchange_mode = e->cfg.nranks > 1 ? SART_EXCHANGE_NCCL : SART_EXCHANGE_NONE;
             f += nf;
         } else {
             int32_t st = 0, it = 0;

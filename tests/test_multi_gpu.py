@@ -44,6 +44,11 @@ def test_sharded_solve_matches_oracle(world):
             if c["iterations2"][0] == c["iterations2"][1]:
                 assert c["x2"] <= 1e-5, (name, c)
             hashes.add(c["x_hash"])
+            if c["batch"] is not None:  # sart_solve_batch against frame-by-frame solves on the same ranks
+                b = c["batch"]
+                assert b["iteration_gap"] <= 1, (name, b)
+                if b["iteration_gap"] == 0:
+                    assert b["same_status"] and b["x"] <= 1e-5, (name, b)
             # the fused sweep reduces over peer memory (one kernel), the two-kernel sweep over NCCL
             import os as _os
             if c["mode"] == 2 and _os.environ.get("SART_EXCHANGE") != "nccl":
@@ -51,6 +56,8 @@ def test_sharded_solve_matches_oracle(world):
             else:
                 assert c["exchange"] == 1, (name, c)
         assert len(hashes) == 1, f"{name}: ranks ended with different solutions"
+        batch_hashes = {r["checks"][name]["batch"]["hash"] for r in ranks if r["checks"][name]["batch"] is not None}
+        assert len(batch_hashes) <= 1, f"{name}: ranks ended with different batch solutions"
 
 
 def test_cpp_solver_driver_on_two_gpus(tmp_path):
