@@ -188,6 +188,21 @@ int sart_get_config(const sart_engine* e, sart_config* out);
 int sart_solve(sart_engine* e, const double* measurement, double* solution, int32_t has_guess, int32_t* status,
                int32_t* iterations);
 
+/* A warm-started time series in one call: the frame loop of source/main.cpp:125-140 (without --no_guess), where every
+ * frame starts from the previous frame's solution. COLLECTIVE.
+ *   measurements [nframes][nrows] (host, double), guess [nvoxel] or NULL (start of frame 0; NULL = default initial
+ *   guess), solutions [nframes][nvoxel] (host, double, out), status / iterations [nframes] or NULL.
+ * Every frame gets what the sequence sart_solve(frame 0), sart_solve(frame 1, has_guess = 1), ... gives, within the
+ * parity tolerance. Knowing the next frame in advance lets the engine save a pass over the matrix per frame: the sweep
+ * predicted to be a frame's last (the previous frame's iteration count, once two consecutive frames agreed to within two
+ * iterations) back-projects the next frame's measurement, so a
+ * frame that stops as predicted hands its successor the first iteration (linear solver, SART_SEMANTICS_CPU, whole-solve
+ * kernel; otherwise the frames are simply solved one after the other). After the call sart_get_stats reports for the
+ * whole series: sweeps = passes over the matrix actually made, fp_launches = frames that received their first iteration
+ * from their predecessor, bp_launches = sweeps that had to be repeated because a frame did not stop where predicted. */
+int sart_solve_series(sart_engine* e, int32_t nframes, const double* measurements, const double* guess, double* solutions,
+                      int32_t* status, int32_t* iterations);
+
 /* Several frames that do NOT start from each other's solutions -- the reference's --no_guess loop, source/main.cpp:131-140
  * with solution_vec.clear() after every frame -- in one call. Such frames are independent right-hand sides of the same
  * matrix, so the engine solves them four at a time: every pass over the matrix (forward projection, back projection)

@@ -31,6 +31,7 @@ SYMBOLS = [
     "sart_set_max_iterations", "sart_set_fixed_iterations", "sart_get_config", "sart_solve", "sart_stage_measurement",
     "sart_stage_guess", "sart_solve_resident", "sart_fetch_solution", "sart_forward_project", "sart_get_stats",
     "sart_kernel_forward", "sart_kernel_backward", "sart_back_project_noalloc", "sart_load_rows_file", "sart_solve_batch",
+    "sart_solve_series",
 ]
 
 
@@ -104,6 +105,7 @@ def lib():
         L.sart_get_config.argtypes = [_vp, C.POINTER(Config)]
         L.sart_solve.argtypes = [_vp, _vp, _vp, _i32, C.POINTER(_i32), C.POINTER(_i32)]
         L.sart_solve_batch.argtypes = [_vp, _i32, _vp, _vp, _vp, _vp]
+        L.sart_solve_series.argtypes = [_vp, _i32, _vp, _vp, _vp, _vp, _vp]
         L.sart_stage_measurement.argtypes = [_vp, _vp]
         L.sart_stage_guess.argtypes = [_vp, _vp]
         L.sart_solve_resident.argtypes = [_vp, _i32, C.POINTER(_i32), C.POINTER(_i32)]
@@ -284,6 +286,21 @@ class Engine:
         st, it = np.zeros(F, dtype=np.int32), np.zeros(F, dtype=np.int32)
         check(lib().sart_solve_batch(self._h, F, g.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p),
                                      st.ctypes.data_as(C.c_void_p), it.ctypes.data_as(C.c_void_p)))
+        return x, st, it
+
+    def solve_series(self, frames, guess=None):
+        """Warm-started series: frame k starts from the solution of frame k - 1 (frame 0 from ``guess`` or the default
+        initial guess). frames [F][nrows] -> (x [F][nvoxel], status [F], iterations [F])."""
+        g = np.ascontiguousarray(np.atleast_2d(frames), dtype=np.float64)
+        if g.shape[1] != self.nrows:
+            raise ValueError(f"each frame must hold this rank's {self.nrows} pixels")
+        F = g.shape[0]
+        x = np.zeros((F, self.nvoxel))
+        st, it = np.zeros(F, dtype=np.int32), np.zeros(F, dtype=np.int32)
+        x0 = None if guess is None else _f64(guess)
+        check(lib().sart_solve_series(self._h, F, g.ctypes.data_as(C.c_void_p),
+                                      None if x0 is None else x0.ctypes.data_as(C.c_void_p), x.ctypes.data_as(C.c_void_p),
+                                      st.ctypes.data_as(C.c_void_p), it.ctypes.data_as(C.c_void_p)))
         return x, st, it
 
     def stage_measurement(self, measurement):

@@ -120,7 +120,15 @@ struct sart_engine {
     bool persistent = false;
     void (*fs_kernel)(const sart::FusedArgs, const sart::SolveArgs) = nullptr;
     uint32_t fs_nclusters = 0;
-    unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer
+    unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer, [4] tails run
+    IterState last_fin{};                       // final state of the last whole-solve launch
+    unsigned long long last_tails = 0;          // sweeps that launch ran
+    int last_prologue_sweeps = 0;               // matrix passes of the last frame's set-up (initial guess, log "obs")
+    // warm-started series (sart_solve_series): look-ahead buffers for the next frame, allocated on first use
+    double* d_gd_next = nullptr;
+    FrameScalars* d_fs_next = nullptr;
+    float* d_gspec = nullptr;
+    double* d_spec_scale = nullptr;
     uint64_t xchg_cta_flag_off = 0;             // per-CTA flags of the in-kernel exchange inside a region
 
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
@@ -354,7 +362,7 @@ int plan_fused(sart_engine* e) {
         e->fs_kernel = sk;
         e->fs_nclusters = e->fu_nclusters;
         e->persistent = coop && env_int("SART_PERSISTENT", 1) != 0;
-        if (e->persistent && !e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 4));
+        if (e->persistent && !e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 8));
     }
     (void)cudaGetLastError();
     return SART_OK;
@@ -469,6 +477,7 @@ UpdArgs make_update_args(sart_engine* e, int t, const IterState* st) {
     u.eps_norm = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 1.e-7 : 0.0;
     u.eps_orig = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 0.0 : 1.e-100;
     u.log_mode = e->cfg.logarithmic;
+    u.out_scale = 1.0;
     return u;
 }
 
@@ -502,7 +511,11 @@ int launch_xchg_update(sart_engine* e, int t, const IterState* st_in, IterState*
 // The whole solve (sweeps 0 .. stop) in ONE cooperative launch of fused_solve_kernel: reduction over clusters and ranks,
 // decision and update run inside the kernel between two grid barriers. cudaErrorCooperativeLaunchTooLarge or an
 // unsupported attribute combination is reported as "not launched" so that the caller can fall back.
-int launch_solve(sart_engine* e, bool* launched) {
+struct SolveLaunch {
+    int t0 = 0, pflip = 0, t_spec = -1;  // see SolveArgs
+};
+
+int launch_solve(sart_engine* e, bool* launched, const SolveLaunch& opt = SolveLaunch()) {
     *launched = false;
     FusedArgs a;
     a.H = e->dH;
@@ -540,7 +553,13 @@ int launch_solve(sart_engine* e, bool* launched) {
     sv.buf_off[0] = e->xchg_buf_off[0];
     sv.buf_off[1] = e->xchg_buf_off[1];
     sv.flag_off = e->xchg_cta_flag_off;
-    CUDA_TRY(cudaMemsetAsync(e->d_solve_ctl, 0, 4 * sizeof(unsigned long long), e->stream));
+    sv.t0 = opt.t0;
+    sv.pflip = opt.pflip;
+    sv.t_spec = opt.t_spec;
+    sv.g_spec = e->d_gspec;
+    sv.out_scale = e->d_spec_scale;
+    sv.exchanges = e->d_solve_ctl + 4;
+    CUDA_TRY(cudaMemsetAsync(e->d_solve_ctl, 0, 8 * sizeof(unsigned long long), e->stream));
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -671,23 +690,26 @@ int launch_prepare(sart_engine* e, int weights_mode) {
 // What follows the whole-solve kernel: final state to the host, un-normalised solution, statistics.
 int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks) {
     if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][3], e->stream));
-    unsigned long long tail[2] = {0, 0};
+    unsigned long long tail[4] = {0, 0, 0, 0};  // tail time (ns), tails timed, scratch, tails run
+    static_assert(sizeof(tail) <= sizeof(IterState), "the second pinned slot carries the control words");
     CUDA_TRY(cudaMemcpyAsync(&e->h_st[0], e->d_st[0], sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaMemcpyAsync(&e->h_st[1], e->d_solve_ctl + 1, sizeof(tail), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaEventRecord(e->ev_batch[0], e->stream));
     CUDA_TRY(cudaEventSynchronize(e->ev_batch[0]));
     const IterState fin = e->h_st[0];
     std::memcpy(tail, &e->h_st[1], sizeof(tail));
+    e->last_fin = fin;
+    e->last_tails = tail[3];
     if (!fin.done) return fail(SART_ERR_STATE, "whole-solve kernel ended without a decision (internal error)");
     if (fin.status == kStatusExchangeTimeout)
         return fail(SART_ERR_NCCL, "in-kernel barrier or peer-memory exchange timed out: a CTA or a rank of the job did not arrive");
-    if (e->cfg.nranks > 1) e->xchg_epoch += (unsigned long long)fin.iterations + 1;  // one exchange per sweep, every rank alike
+    if (e->cfg.nranks > 1) e->xchg_epoch += tail[3];  // one exchange per sweep run, every rank alike
 
     finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_xd[0], e->d_xd[1], e->d_st[0], e->d_fs, e->d_xio, e->V);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
 
-    const int nsweeps = fin.iterations + 1;  // sweeps 0 .. iterations, all of them inside the one launch
+    const int nsweeps = (int)tail[3];  // sweeps run inside the one launch (iterations + 1 for a solve of its own)
     e->stats.status = fin.status;
     e->stats.iterations = fin.iterations;
     e->stats.sweeps = sweeps_before + 2 * fin.iterations + 1;
@@ -710,7 +732,9 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
 }
 
 // The whole solve from device-resident inputs (d_gd, and d_xio when has_guess) to device-resident output (d_xio).
-int run_solve(sart_engine* e, int has_guess) {
+// Per-frame set-up from the staged measurement d_gd (and d_xio when has_guess): statistics, normalisation, starting
+// solution into buffer 0, fresh control blocks. *sweeps counts the matrix passes it took (initial guess, log "obs").
+int frame_prologue(sart_engine* e, int has_guess, int* sweeps) {
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
     const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
     const bool log_mode = e->cfg.logarithmic != 0;
@@ -721,19 +745,19 @@ int run_solve(sart_engine* e, int has_guess) {
     SART_TRY(allreduce_f64(e, &e->d_fs->gmax, 1, ncclMax));
     SART_TRY(allreduce_f64(e, &e->d_fs->gsq, 1, ncclSum));
 
-    int sweeps = 0;
+    *sweeps = 0;
     if (log_mode) {
         SART_TRY(launch_prepare(e, 3));
         SART_TRY(backproject_weights(e));
         mask_obs_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_rho, e->cfg.ray_density_threshold, e->d_obs, e->V);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
-        ++sweeps;
+        ++*sweeps;
     }
     SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1)));
     if (!has_guess) {
         SART_TRY(backproject_weights(e));
-        ++sweeps;
+        ++*sweeps;
     }
     // lower clamp of the starting solution: GPU semantics 1e-7 (normalised units) for both solvers
     // (sartsolver_cuda.cpp:180); CPU semantics 1e-100 (caller units) for the log solver only (sartsolver.cpp:263)
@@ -747,6 +771,14 @@ int run_solve(sart_engine* e, int has_guess) {
     init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_st[0], e->d_st[1]);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
+    return SART_OK;
+}
+
+int run_solve(sart_engine* e, int has_guess) {
+    const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
+    int sweeps = 0;
+    SART_TRY(frame_prologue(e, has_guess, &sweeps));
+    e->last_prologue_sweeps = sweeps;
     CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
 
     if (e->fused && e->persistent && (e->cfg.nranks <= 1 || e->peer_exchange)) {
@@ -1236,6 +1268,9 @@ void free_engine(sart_engine* e) {
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
+    void* series_ptrs[] = {e->d_gd_next, e->d_fs_next, e->d_gspec, e->d_spec_scale};
+    for (void* p : series_ptrs)
+        if (p) cudaFree(p);
     void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
                          e->d_pg, e->d_pw, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
     for (void* p : pair_ptrs)
@@ -1680,6 +1715,133 @@ int sart_solve(sart_engine* e, const double* measurement, double* solution, int3
     if (status) *status = e->stats.status;
     if (iterations) *iterations = e->stats.iterations;
     return SART_OK;
+}
+
+// A warm-started series in one call (the frame loop of source/main.cpp:125-140 without --no_guess). Frame by frame as
+// sart_solve would do it, except that -- when the whole-solve kernel runs (linear solver, CPU semantics) -- the sweep
+// that is predicted to be a frame's last one (the previous frame's iteration count) back-projects the NEXT frame's
+// measurement: that sweep evaluates the frame's final iterate anyway, and its forward projection is, up to the ratio
+// of the two normalisations, the next frame's first one. A frame that stops as predicted therefore hands the next
+// frame its first update and saves it one pass over the matrix (2 instead of 3 for a frame that needs two iterations);
+// a frame that does not stop there repeats that sweep with its own measurement (one pass lost).
+static int solve_series_impl(sart_engine* e, int32_t nframes, const double* measurements, const double* guess, double* solutions,
+                      int32_t* status, int32_t* iterations) {
+    const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256), pblocks = (uint32_t)ceil_div(e->P, 256);
+    const bool whole = e->fused && e->persistent && (e->cfg.nranks <= 1 || e->peer_exchange);
+    const bool speculate = whole && !e->cfg.logarithmic && e->cfg.semantics == SART_SEMANTICS_CPU &&
+                           env_int("SART_SERIES_LOOKAHEAD", 1) != 0;
+    if (speculate && !e->d_gd_next) {
+        SART_TRY(dev_alloc(&e->d_gd_next, e->P));
+        SART_TRY(dev_alloc(&e->d_fs_next, 1));
+        SART_TRY(dev_alloc(&e->d_gspec, e->P));
+        SART_TRY(dev_alloc(&e->d_spec_scale, 1));
+    }
+    e->launches = 0;
+    CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
+    uint64_t h2d = 0, d2h = 0;
+    int total_sweeps = 0, total_fused = 0, handed_frames = 0, repeated = 0;
+    if (nframes > 0) {
+        CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurements, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+        h2d += e->P * sizeof(double);
+        if (guess) {
+            CUDA_TRY(cudaMemcpyAsync(e->d_xio, guess, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+            h2d += e->V * sizeof(double);
+        }
+    }
+    bool handed = false;
+    int it_prev = -1, it_prev2 = -1, pflip_next = 0;
+    for (int32_t f = 0; f < nframes; ++f) {
+        const int has_guess = (f > 0 || guess) ? 1 : 0;
+        const bool more = f + 1 < nframes;
+        if (!speculate) {
+            if (f > 0) {
+                CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurements + (uint64_t)f * e->P, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+                h2d += e->P * sizeof(double);
+            }
+            SART_TRY(run_solve(e, has_guess));
+            // passes over the matrix: set-up + one per iterate with the fused sweep, two per iteration without
+            const int it = e->stats.iterations;
+            total_sweeps += e->last_prologue_sweeps + (e->stats.sweep_mode == SART_SWEEP_FUSED ? it + 1 : 2 * it + 1);
+            total_fused += e->stats.fused_launches;
+        } else {
+            SolveLaunch opt;
+            int sweeps = 0;
+            if (!handed) {
+                SART_TRY(frame_prologue(e, has_guess, &sweeps));
+            } else {
+                // the previous frame's last sweep already did this frame's first iteration; its statistics were reduced then
+                SART_TRY(launch_prepare(e, 0));
+                init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_st[0], e->d_st[1]);
+                CUDA_TRY(cudaGetLastError());
+                ++e->launches;
+                opt.t0 = 1;
+                opt.pflip = pflip_next;
+            }
+            if (more) {
+                CUDA_TRY(cudaMemcpyAsync(e->d_gd_next, measurements + (uint64_t)(f + 1) * e->P, e->P * sizeof(double),
+                                         cudaMemcpyHostToDevice, e->stream));
+                h2d += e->P * sizeof(double);
+                // predict "stops where the previous frame stopped" once two consecutive frames agreed to within two iterations
+                if (it_prev >= 2 && it_prev2 >= 2 && std::abs(it_prev - it_prev2) <= 2) {
+                    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_gd_next, e->P, e->d_fs_next);
+                    CUDA_TRY(cudaGetLastError());
+                    SART_TRY(allreduce_f64(e, &e->d_fs_next->gmax, 1, ncclMax));
+                    SART_TRY(allreduce_f64(e, &e->d_fs_next->gsq, 1, ncclSum));
+                    series_lookahead_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_gd_next, e->P, e->d_fs, e->d_fs_next, e->d_gspec,
+                                                                            e->d_spec_scale);
+                    CUDA_TRY(cudaGetLastError());
+                    e->launches += 2;
+                    opt.t_spec = it_prev;
+                }
+            }
+            CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
+            if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][2], e->stream));
+            bool launched = false;
+            SART_TRY(launch_solve(e, &launched, opt));
+            if (!launched) return fail(SART_ERR_CUDA, "the device refused the cooperative launch of the whole-solve kernel in the middle of a series");
+            SART_TRY(finish_persistent_solve(e, sweeps, vblocks));
+            const IterState fin = e->last_fin;
+            handed = fin.pad == 1;
+            if (handed) {
+                pflip_next = ((fin.iterations + 1 + opt.pflip) & 1) ^ 1;  // so that the next frame's sweep 1 reads what was just written
+                std::swap(e->d_fs, e->d_fs_next);
+                ++handed_frames;
+            }
+            if ((int)e->last_tails > fin.iterations - opt.t0 + 1) ++repeated;  // a sweep ran twice
+            if (more) std::swap(e->d_gd, e->d_gd_next);
+            it_prev2 = it_prev;
+            it_prev = fin.iterations;
+            total_sweeps += sweeps + (int)e->last_tails;
+            total_fused += (int)e->last_tails;
+        }
+        if (status) status[f] = e->stats.status;
+        if (iterations) iterations[f] = e->stats.iterations;
+        CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)f * e->V, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+        d2h += e->V * sizeof(double) + 2 * sizeof(IterState);
+    }
+    CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+    CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+    float ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
+    e->stats.solve_ms = ms;
+    e->stats.gpu_launches = e->launches;
+    e->stats.h2d_bytes = h2d;
+    e->stats.d2h_bytes = d2h;
+    e->stats.sweeps = total_sweeps;          // matrix passes actually made over the whole series
+    e->stats.fused_launches = total_fused;
+    e->stats.fp_launches = handed_frames;    // frames that received their first iteration from the previous frame
+    e->stats.bp_launches = repeated;         // sweeps run twice because a frame did not stop where predicted
+    e->measurement_staged = nframes > 0;
+    e->guess_staged = nframes > 0;
+    return SART_OK;
+}
+
+int sart_solve_series(sart_engine* e, int32_t nframes, const double* measurements, const double* guess, double* solutions,
+                      int32_t* status, int32_t* iterations) {
+    SART_TRY(require(e, true));
+    if (nframes < 0 || (nframes > 0 && (!measurements || !solutions)))
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_solve_series: NULL buffers or negative frame count");
+    return solve_series_impl(e, nframes, measurements, guess, solutions, status, iterations);
 }
 
 int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements, double* solutions, int32_t* status,

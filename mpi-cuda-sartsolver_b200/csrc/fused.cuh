@@ -155,7 +155,7 @@ __device__ __forceinline__ float lds32(uint32_t addr) {
 // within a launch. A barrier or a peer that does not arrive within ~4 s ends the solve with SART_STATUS_EXCHANGE_TIMEOUT.
 struct SolveArgs {
     IterState* st[2];      // [0] is read on entry; the final state is written to both copies
-    float* xf[2];          // fp32 iterate: sweep t reads xf[t & 1], its tail writes xf[(t + 1) & 1]
+    float* xf[2];          // fp32 iterate: sweep t reads xf[(t + pflip) & 1], its tail writes the other one
     double* xd[2];         // fp64 master copy, same parity rule
     UpdArgs upd;           // constant fields of the update (xd_cur / xd_next / xf_next / sred / st are set per sweep)
     double tol;
@@ -167,6 +167,16 @@ struct SolveArgs {
     unsigned long long epoch0;  // sweep t uses epoch0 + t + 1
     uint64_t buf_off[2];   // byte offsets of the two exchange buffers inside a region
     uint64_t flag_off;     // byte offset of the per-CTA flags [nranks][gridDim.x] inside a region
+    // Warm-started series (sart_solve_series): sweep t0 is the first one (1 when the previous frame's last sweep already
+    // produced this frame's first update), buffers are indexed by (t + pflip) & 1, and at sweep t_spec (-1: never) the
+    // back projection uses g_spec -- the NEXT frame's measurement in this frame's normalisation -- instead of g: if the
+    // solve stops there, as predicted, that sweep has at the same time evaluated this frame's last iterate and done the
+    // next frame's first iteration (out_scale converts it to the next frame's normalisation); if it does not stop, the
+    // sweep is run again with this frame's own measurement.
+    int t0, pflip, t_spec;
+    const float* g_spec;
+    const double* out_scale;  // device scalar: this frame's norm / the next frame's norm
+    unsigned long long* exchanges;  // number of tails run (= exchanges over the ranks), written at the end
     unsigned long long* tail_ns;  // [3], zero at launch: ns CTA 0 spent between the end of a sweep (first grid barrier passed) and the start of the next, how often, scratch
 };
 
@@ -273,9 +283,20 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0, fin_stage = 0, fin_slot = 0, fin_parity = 0;  // consumers
     unsigned long long bar_target = 0;
 
-    for (int t = 0;; ++t) {
+    int t_spec = -1, pflip = 0;
+    bool repeated = false;
+    unsigned long long tails = 0;
+    if constexpr (PERSIST) {
+        t_spec = sv->t_spec;
+        pflip = sv->pflip;
+    }
+    for (int t = PERSIST ? sv->t0 : 0;; ++t) {
         const float* xcur = a.x;
-        if constexpr (PERSIST) xcur = sv->xf[t & 1];
+        const float* gsrc = a.g;
+        if constexpr (PERSIST) {
+            xcur = sv->xf[(t + pflip) & 1];
+            if (t == t_spec) gsrc = sv->g_spec;
+        }
 
         if (warp == NWC) {
             // ---- producer --------------------------------------------------------------------------------------------
@@ -334,7 +355,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             auto load_batch = [&](uint32_t t0) {
                 const uint32_t row = t0 + lane;
                 const uint64_t off = (uint64_t)cid + (uint64_t)row * ncl;
-                g_nxt = (row < n) ? __ldg(a.g + off) : 0.f;
+                g_nxt = (row < n) ? __ldg(gsrc + off) : 0.f;
                 r_nxt = (row < n) ? __ldg(a.rinv + off) : 0.f;
             };
             const uint32_t c4 = (C + 3) / 4;  // 128-bit loads that cover the C per-CTA sums
@@ -459,7 +480,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 if (lane == 0) s_f2 = f;
             }
             const bool multi = sv->nranks > 1;
-            const unsigned long long epoch = sv->epoch0 + (unsigned long long)t + 1;
+            const unsigned long long epoch = sv->epoch0 + (++tails);  // one exchange per tail, repeated sweeps included
             const uint64_t rec = (uint64_t)blk * (chunk + 1);  // this CTA's record in an exchange buffer: [sum(fit^2)][chunk]
             if (ok && multi) {
                 double* mine = reinterpret_cast<double*>(sv->peers[sv->rank] + sv->buf_off[epoch & 1]) + rec;
@@ -492,6 +513,8 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 atomicAdd(sv->gbar, kBarrierPoison);  // nobody waits for this CTA again
                 stop = true;
                 status = kStatusExchangeTimeout;
+            } else if (repeated) {
+                repeated = false;  // sweep t run again after a wrong prediction: "continue" was decided the first time
             } else if (t >= 1) {
                 double f2 = s_f2;
                 if (multi) {
@@ -509,36 +532,42 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 }
                 conv_prev = conv;
             }
-            if (stop) {
-                if ((blk == 0 || !ok) && tid == 0) {
-                    IterState o;
-                    o.conv_prev = conv_prev;
-                    o.k = t;
-                    o.done = 1;
-                    o.status = status;
-                    o.iterations = t;
-                    o.final_buf = t & 1;
-                    o.pad = 0;
-                    *sv->st[0] = o;
-                    *sv->st[1] = o;
-                }
-                break;
+            const bool spec = ok && (t == t_spec);
+            const bool hand_over = spec && stop;  // predicted stop: this sweep's back projection is the next frame's first
+            const bool redo = spec && !stop;      // wrong prediction: the sweep has to be run again with this frame's own g
+            if (stop && (blk == 0 || !ok) && tid == 0) {
+                IterState o;
+                o.conv_prev = conv_prev;
+                o.k = t;
+                o.done = 1;
+                o.status = status;
+                o.iterations = t;
+                o.final_buf = (t + pflip) & 1;
+                o.pad = hand_over ? 1 : 0;
+                *sv->st[0] = o;
+                *sv->st[1] = o;
+                *sv->exchanges = tails;
             }
-            UpdArgs u = sv->upd;
-            u.xd_cur = sv->xd[t & 1];
-            u.xd_next = sv->xd[(t + 1) & 1];
-            u.xf_next = sv->xf[(t + 1) & 1];
-            for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) {
-                double sj;
-                if (multi) {
-                    sj = 0.0;
-                    for (uint32_t r = 0; r < sv->nranks; ++r)
-                        sj += __ldcv(reinterpret_cast<const double*>(sv->peers[r] + sv->buf_off[epoch & 1]) + rec + 1 + (j - j0));
-                } else {
-                    sj = local_sum(j);
+            if (stop && !hand_over) break;
+            if (!redo) {
+                UpdArgs u = sv->upd;
+                u.xd_cur = sv->xd[(t + pflip) & 1];
+                u.xd_next = sv->xd[(t + 1 + pflip) & 1];
+                u.xf_next = sv->xf[(t + 1 + pflip) & 1];
+                u.out_scale = hand_over ? *sv->out_scale : 1.0;
+                for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) {
+                    double sj;
+                    if (multi) {
+                        sj = 0.0;
+                        for (uint32_t r = 0; r < sv->nranks; ++r)
+                            sj += __ldcv(reinterpret_cast<const double*>(sv->peers[r] + sv->buf_off[epoch & 1]) + rec + 1 + (j - j0));
+                    } else {
+                        sj = local_sum(j);
+                    }
+                    apply_update(u, j, sj);
                 }
-                apply_update(u, j, sj);
             }
+            if (hand_over) break;
             bar_target += nblk;
             if (!grid_barrier(sv->gbar, bar_target, &s_abort)) {
                 if (tid == 0) {
@@ -548,16 +577,22 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     o.done = 1;
                     o.status = kStatusExchangeTimeout;
                     o.iterations = t;
-                    o.final_buf = t & 1;
+                    o.final_buf = (t + pflip) & 1;
                     o.pad = 0;
                     *sv->st[0] = o;
                     *sv->st[1] = o;
+                    *sv->exchanges = tails;
                 }
                 break;
             }
             if (blk == 0 && tid == 0) {
                 sv->tail_ns[0] += global_timer_ns() - sv->tail_ns[2];
                 sv->tail_ns[1] += 1;
+            }
+            if (redo) {  // the partials of this sweep have been read by everyone (barrier above): run sweep t again
+                t_spec = -1;
+                repeated = true;
+                --t;
             }
         }
     }

@@ -521,6 +521,7 @@ struct UpdArgs {
     double beta, relax, h_d;
     double eps_norm, eps_orig;  // log solver's epsilon: in normalised units (GPU semantics) or caller units (CPU, 1e-100)
     int log_mode;
+    double out_scale;           // 1, or the factor into the next frame's normalisation (series hand-over, fused.cuh)
 };
 
 // x_{t+1,j} from x_t and the reduced back projection s_j of voxel j. x_t is read through L2 (ld.global.cg): in the
@@ -546,6 +547,7 @@ __device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, doubl
         const double eps = a.eps_norm + a.eps_orig / a.fs->norm;
         xn = __ldcg(a.xd_cur + j) * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
     }
+    xn *= a.out_scale;
     a.xd_next[j] = xn;
     a.xf_next[j] = (float)xn;
 }
@@ -736,6 +738,17 @@ __global__ void frame_prepare_kernel(const double* __restrict__ gd, uint64_t P, 
     if (weights_mode == 1) w[i] = gi;
     else if (weights_mode == 2) w[i] = (gi > 0.f) ? gi : 0.f;
     else if (weights_mode == 3) w[i] = (gi >= 0.f) ? gi * ri : 0.f;
+}
+
+// Series look-ahead (sart_solve_series): the NEXT frame's measurement in the CURRENT frame's normalisation, which the
+// last sweep of the current frame back-projects instead of its own measurement, and the factor that converts the update
+// it produces into the next frame's normalisation. Saturated pixels stay negative (the norm is positive).
+__global__ void series_lookahead_kernel(const double* __restrict__ g_next, uint64_t P, const FrameScalars* cur,
+                                        const FrameScalars* next, float* __restrict__ g_spec, double* __restrict__ scale) {
+    const double norm = cur->norm;
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *scale = norm / ((next->gmax > 0) ? next->gmax : 1.0);
+    if (i < P) g_spec[i] = (float)(g_next[i] / norm);
 }
 
 // Starting solution. from_guess: x = caller's solution / norm (sartsolver_cuda.cpp:176-178); else the default

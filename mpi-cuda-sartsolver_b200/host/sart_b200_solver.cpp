@@ -284,6 +284,28 @@ int main(int argc, char* argv[]) {
                 store(k + b, group_solutions.data() + b * nvoxel, status[b], iterations[b]);
                 flush(k + b + 1);
             }
+        } else if (!config.no_guess && frames->size() - k >= 2) {
+            // warm-started frames in chunks of max_cached_frames (the reference's frame cache, source/image.cpp:268-331):
+            // sart_solve_series knows the next frame while it solves the current one
+            const size_t nc = std::min<size_t>((size_t)config.max_cached_frames, frames->size() - k);
+            std::vector<double> chunk(nc * npixel_local), chunk_solutions(nc * nvoxel), one;
+            for (size_t b = 0; b < nc; ++b) {
+                if (!frames->read(k + b, offset_pixel, npixel_local, one, error)) die(error);
+                std::copy(one.begin(), one.end(), chunk.begin() + b * npixel_local);
+            }
+            const auto last = std::chrono::steady_clock::now();
+            std::vector<int32_t> status(nc, 0), iterations(nc, 0);
+            must(sart_solve_series(engine, (int32_t)nc, chunk.data(), solution_vec.empty() ? nullptr : solution_vec.data(),
+                                   chunk_solutions.data(), status.data(), iterations.data()));
+            const std::chrono::duration<double, std::milli> duration(std::chrono::steady_clock::now() - last);
+            for (size_t b = 0; b < nc; ++b) {
+                if (rank == 0) std::cout << "Processed in: " << duration.count() / (double)nc << " ms" << std::endl;
+                store(k + b, chunk_solutions.data() + b * nvoxel, status[b], iterations[b]);
+                flush(k + b + 1);
+            }
+            solution_vec.assign(chunk_solutions.end() - (std::ptrdiff_t)nvoxel, chunk_solutions.end());
+            k += nc;
+            continue;
         } else {
             if (!frames->read(k, offset_pixel, npixel_local, frame, error)) die(error);
             const auto last = std::chrono::steady_clock::now();

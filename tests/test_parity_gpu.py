@@ -516,3 +516,59 @@ def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, sart, res
             assert stb[f] == st_ref and rel_l2(xb[f], x_ref) <= TOL
     if tol is not None:
         assert len(set(itb.tolist())) > 1  # the frames really stopped at different iterations
+
+
+@pytest.mark.parametrize("P,V,tol,kind", [(3000, 4100, 1e-4, "steady"), (900, 20000, 1e-4, "steady"), (2048, 640, 1e-5, "drift")])
+def test_warm_started_series_with_lookahead_matches_frame_by_frame(P, V, tol, kind, sart, restatement, monkeypatch):
+    """sart_solve_series against the same frames solved one by one with a warm start (same engine, look-ahead off) and
+    against the oracle's sequence: same status, stopping iteration within one, solutions within the parity tolerance --
+    while the look-ahead saves a pass over the matrix for every frame that stops where its predecessor did.
+    "steady": nearly identical frames (a few iterations each once warm) with one jump that breaks the prediction;
+    "drift": a moving profile whose frames need many, changing iteration counts (predictions rarely apply)."""
+    syn = load_synthetic()
+    H = restatement.fill_synthetic(P, V, 77)
+    F = 10
+    if kind == "steady":
+        g0 = restatement.forward(H, syn.emission_profile(V))
+        frames = np.stack([g0 * (1.0 + 1e-3 * k) for k in range(F)])
+    else:
+        frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=0.02 * k)) * (1.0 + 0.1 * k) for k in range(F)])
+    frames[:, ::23] = -1.0  # saturated pixels in every frame
+    frames[6] *= 3.0       # a jump: this frame needs more iterations than its predecessor
+    lap = syn.laplacian_coo(V)
+    kw = dict(beta_laplace=2e-2, max_iterations=200, conv_tolerance=tol, sweep_mode=FUSED)
+    out = {}
+    for look in ("1", "0"):
+        monkeypatch.setenv("SART_SERIES_LOOKAHEAD", look)
+        with sart.Engine(P, V, device=0, **kw) as eng:
+            eng.upload_rows(H)
+            eng.set_laplacian(*lap)
+            eng.finalize()
+            xs, sts, its = eng.solve_series(frames)
+            s = eng.stats()
+            out[look] = (xs, sts, its, s.sweeps, s.fp_launches, s.bp_launches)
+            if look == "0":
+                x1 = [eng.solve(frames[0])]
+                for k in range(1, F):
+                    x1.append(eng.solve(frames[k], x1[-1][0]))
+    xs, sts, its, sweeps, handed, repeated = out["1"]
+    xs0, sts0, its0, sweeps0, handed0, repeated0 = out["0"]
+    assert handed0 == 0 and repeated0 == 0
+    for k in range(F):  # look-ahead off == plain warm-started solves, bit for bit
+        assert np.array_equal(xs0[k], x1[k][0]) and (sts0[k], its0[k]) == x1[k][1:]
+    x_prev = None
+    for k in range(F):
+        assert sts[k] == sts0[k] and abs(int(its[k]) - int(its0[k])) <= 1
+        if its[k] == its0[k]:
+            assert rel_l2(xs[k], xs0[k]) <= TOL
+        okw = dict(lap=lap, beta_laplace=2e-2, max_iterations=200, conv_tolerance=tol)
+        x_ref, st_ref, it_ref = restatement.solve(H, frames[k], x0=x_prev, **okw)
+        x_prev = x_ref
+        assert sts[k] == st_ref and abs(int(its[k]) - it_ref) <= 1
+        if its[k] == it_ref:
+            assert rel_l2(xs[k], x_ref) <= TOL
+    # passes over the matrix: initial guess + one per iterate of every frame, minus the handed-over first iterations
+    assert sweeps == 1 + int(np.sum(its + 1)) - handed + repeated
+    if kind == "steady":
+        assert handed >= 2 and repeated >= 1, (its.tolist(), handed, repeated)
+    assert sweeps0 == 1 + int(np.sum(its0 + 1))

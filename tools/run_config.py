@@ -40,6 +40,8 @@ def main():
     ap.add_argument("--iterations", type=int, default=5)
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the row count (debugging on fewer GPUs)")
     ap.add_argument("--sweep", default="auto", choices=["auto", "split", "fused"])
+    ap.add_argument("--series", action="store_true",
+                    help="c4: hand the whole series to sart_solve_series (look-ahead) instead of one resident solve per frame")
     ap.add_argument("--batch", type=int, default=0,
                     help="c2: solve this many independent frames (no warm start, --iterations each) with sart_solve_batch "
                          "and one by one, and report both rates")
@@ -115,7 +117,13 @@ def main():
         t1 = time.perf_counter()
         dev_ms = 0.0
         x = None
-        for f in range(F):
+        if args.series:
+            xs_all, sts, its = eng.solve_series(frames)
+            ss = eng.stats()
+            x, iters, statuses, dev_ms = xs_all[-1], [int(v) for v in its], [int(v) for v in sts], ss.solve_ms
+            out.update({"series_call": True, "matrix_passes": ss.sweeps, "frames_handed_their_first_iteration": ss.fp_launches,
+                        "sweeps_repeated": ss.bp_launches})
+        for f in range(0 if not args.series else F, F):
             eng.stage_measurement(frames[f])
             st, it = eng.solve_resident(f > 0)  # warm start from the previous solution, left on the device
             x = eng.fetch_solution()            # what main() hands to the solution writer
