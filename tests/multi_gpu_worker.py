@@ -76,8 +76,23 @@ def main():
                      "same_status": bool(all(int(stb[k]) == singles[k][1] for k in range(5))),
                      "iteration_gap": int(max(abs(int(itb[k]) - singles[k][2]) for k in range(5))),
                      "hash": float(np.sum(xb[4] * np.arange(1, V + 1)))}
+        # warm-started series through sart_solve_series (look-ahead) against solve-by-solve on the same ranks
+        series = None
+        if not kw.get("logarithmic"):
+            frames = np.stack([(1.0 + 1e-3 * k) * g[off:off + n] for k in range(7)])
+            xs, sts, its = eng.solve_series(frames)
+            handed = eng.stats().fp_launches
+            prev, worst, same = None, 0.0, True
+            for k in range(7):
+                prev = eng.solve(frames[k]) if prev is None else eng.solve(frames[k], prev[0])
+                same = same and int(sts[k]) == prev[1] and abs(int(its[k]) - prev[2]) <= 1
+                if int(its[k]) == prev[2]:
+                    worst = max(worst, rel_l2(xs[k], prev[0]))
+            series = {"x": worst, "consistent": bool(same), "handed": int(handed),
+                      "hash": float(np.sum(xs[-1] * np.arange(1, V + 1)))}
         eng.close()
         out["checks"][name] = {
+            "series": series,
             "batch": batch,
             "rho": rel_l2(rho, rho_ref), "lam": rel_l2(lam, lam_ref[off:off + n]),
             "x": rel_l2(x, x_ref), "status": [st, st_ref], "iterations": [it, it_ref],

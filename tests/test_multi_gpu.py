@@ -49,6 +49,8 @@ def test_sharded_solve_matches_oracle(world):
                 assert b["iteration_gap"] <= 1, (name, b)
                 if b["iteration_gap"] == 0:
                     assert b["same_status"] and b["x"] <= 1e-5, (name, b)
+            if c["series"] is not None:  # sart_solve_series against warm-started solves on the same ranks
+                assert c["series"]["consistent"] and c["series"]["x"] <= 1e-5, (name, c["series"])
             # the fused sweep reduces over peer memory (one kernel), the two-kernel sweep over NCCL
             import os as _os
             if c["mode"] == 2 and _os.environ.get("SART_EXCHANGE") != "nccl":
@@ -58,6 +60,8 @@ def test_sharded_solve_matches_oracle(world):
         assert len(hashes) == 1, f"{name}: ranks ended with different solutions"
         batch_hashes = {r["checks"][name]["batch"]["hash"] for r in ranks if r["checks"][name]["batch"] is not None}
         assert len(batch_hashes) <= 1, f"{name}: ranks ended with different batch solutions"
+        series_hashes = {r["checks"][name]["series"]["hash"] for r in ranks if r["checks"][name]["series"] is not None}
+        assert len(series_hashes) <= 1, f"{name}: ranks ended with different series solutions"
 
 
 def test_cpp_solver_driver_on_two_gpus(tmp_path):
