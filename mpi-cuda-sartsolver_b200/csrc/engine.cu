@@ -121,14 +121,16 @@ struct sart_engine {
     void (*fs_kernel)(const sart::FusedArgs, const sart::SolveArgs) = nullptr;
     uint32_t fs_nclusters = 0;
     unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer, [4] tails run
-    IterState last_fin{};                       // final state of the last whole-solve launch
-    unsigned long long last_tails = 0;          // sweeps that launch ran
     int last_prologue_sweeps = 0;               // matrix passes of the last frame's set-up (initial guess, log "obs")
     // warm-started series (sart_solve_series): look-ahead buffers for the next frame, allocated on first use
-    double* d_gd_next = nullptr;
+    double* d_series_in = nullptr;    // [capacity][P] the chunk's measurements, uploaded once
     FrameScalars* d_fs_next = nullptr;
     float* d_gspec = nullptr;
     double* d_spec_scale = nullptr;
+    SeriesCtl* d_series_ctl = nullptr;
+    double* d_series_out = nullptr;   // [capacity][V] solutions of a chunk, copied to the caller at the end
+    int* d_series_res = nullptr;      // [2][capacity] status, iterations
+    int32_t series_capacity = 0;
     uint64_t xchg_cta_flag_off = 0;             // per-CTA flags of the in-kernel exchange inside a region
 
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
@@ -511,11 +513,14 @@ int launch_xchg_update(sart_engine* e, int t, const IterState* st_in, IterState*
 // The whole solve (sweeps 0 .. stop) in ONE cooperative launch of fused_solve_kernel: reduction over clusters and ranks,
 // decision and update run inside the kernel between two grid barriers. cudaErrorCooperativeLaunchTooLarge or an
 // unsupported attribute combination is reported as "not launched" so that the caller can fall back.
-struct SolveLaunch {
-    int t0 = 0, pflip = 0, t_spec = -1;  // see SolveArgs
+struct SeriesLaunch {  // one frame of sart_solve_series (see SolveArgs)
+    SeriesCtl* ctl = nullptr;
+    int has_next = 0;
+    int* out_status = nullptr;
+    int* out_iterations = nullptr;
 };
 
-int launch_solve(sart_engine* e, bool* launched, const SolveLaunch& opt = SolveLaunch()) {
+int launch_solve(sart_engine* e, bool* launched, const SeriesLaunch& series = SeriesLaunch()) {
     *launched = false;
     FusedArgs a;
     a.H = e->dH;
@@ -553,9 +558,10 @@ int launch_solve(sart_engine* e, bool* launched, const SolveLaunch& opt = SolveL
     sv.buf_off[0] = e->xchg_buf_off[0];
     sv.buf_off[1] = e->xchg_buf_off[1];
     sv.flag_off = e->xchg_cta_flag_off;
-    sv.t0 = opt.t0;
-    sv.pflip = opt.pflip;
-    sv.t_spec = opt.t_spec;
+    sv.series = series.ctl;
+    sv.has_next = series.has_next;
+    sv.out_status = series.out_status;
+    sv.out_iterations = series.out_iterations;
     sv.g_spec = e->d_gspec;
     sv.out_scale = e->d_spec_scale;
     sv.exchanges = e->d_solve_ctl + 4;
@@ -679,9 +685,9 @@ int backproject_weights(sart_engine* e) {
     return SART_OK;
 }
 
-int launch_prepare(sart_engine* e, int weights_mode) {
+int launch_prepare(sart_engine* e, int weights_mode, const double* gd) {
     frame_prepare_kernel<<<(uint32_t)ceil_div(e->P, 256), 256, 0, e->stream>>>(
-        e->d_gd, e->P, e->d_fs, e->d_lambda, e->cfg.ray_length_threshold, e->d_g, e->d_rinv, e->d_w, weights_mode);
+        gd, e->P, e->d_fs, e->d_lambda, e->cfg.ray_length_threshold, e->d_g, e->d_rinv, e->d_w, weights_mode);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
@@ -698,8 +704,6 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
     CUDA_TRY(cudaEventSynchronize(e->ev_batch[0]));
     const IterState fin = e->h_st[0];
     std::memcpy(tail, &e->h_st[1], sizeof(tail));
-    e->last_fin = fin;
-    e->last_tails = tail[3];
     if (!fin.done) return fail(SART_ERR_STATE, "whole-solve kernel ended without a decision (internal error)");
     if (fin.status == kStatusExchangeTimeout)
         return fail(SART_ERR_NCCL, "in-kernel barrier or peer-memory exchange timed out: a CTA or a rank of the job did not arrive");
@@ -734,12 +738,14 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
 // The whole solve from device-resident inputs (d_gd, and d_xio when has_guess) to device-resident output (d_xio).
 // Per-frame set-up from the staged measurement d_gd (and d_xio when has_guess): statistics, normalisation, starting
 // solution into buffer 0, fresh control blocks. *sweeps counts the matrix passes it took (initial guess, log "obs").
-int frame_prologue(sart_engine* e, int has_guess, int* sweeps) {
+// gd: the frame's raw measurement on the device (default: the staging buffer d_gd).
+int frame_prologue(sart_engine* e, int has_guess, int* sweeps, const SeriesCtl* series = nullptr, const double* gd = nullptr) {
+    if (!gd) gd = e->d_gd;
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
     const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
     const bool log_mode = e->cfg.logarithmic != 0;
 
-    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_gd, e->P, e->d_fs);
+    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(gd, e->P, e->d_fs);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     SART_TRY(allreduce_f64(e, &e->d_fs->gmax, 1, ncclMax));
@@ -747,14 +753,14 @@ int frame_prologue(sart_engine* e, int has_guess, int* sweeps) {
 
     *sweeps = 0;
     if (log_mode) {
-        SART_TRY(launch_prepare(e, 3));
+        SART_TRY(launch_prepare(e, 3, gd));
         SART_TRY(backproject_weights(e));
         mask_obs_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_rho, e->cfg.ray_density_threshold, e->d_obs, e->V);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
         ++*sweeps;
     }
-    SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1)));
+    SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1), gd));
     if (!has_guess) {
         SART_TRY(backproject_weights(e));
         ++*sweeps;
@@ -765,7 +771,7 @@ int frame_prologue(sart_engine* e, int has_guess, int* sweeps) {
     const double floor_orig = (!gpu_sem && log_mode) ? 1.e-100 : 0.0;
     start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_xio, e->d_rho, e->cfg.ray_density_threshold,
                                                           e->d_fs, floor_norm, floor_orig, has_guess, e->d_xd[0],
-                                                          e->d_xf[0], e->V);
+                                                          e->d_xf[0], e->V, series);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_st[0], e->d_st[1]);
@@ -1268,7 +1274,7 @@ void free_engine(sart_engine* e) {
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
-    void* series_ptrs[] = {e->d_gd_next, e->d_fs_next, e->d_gspec, e->d_spec_scale};
+    void* series_ptrs[] = {e->d_series_in, e->d_fs_next, e->d_gspec, e->d_spec_scale, e->d_series_ctl, e->d_series_out, e->d_series_res};
     for (void* p : series_ptrs)
         if (p) cudaFree(p);
     void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
@@ -1719,119 +1725,141 @@ int sart_solve(sart_engine* e, const double* measurement, double* solution, int3
 
 // A warm-started series in one call (the frame loop of source/main.cpp:125-140 without --no_guess). Frame by frame as
 // sart_solve would do it, except that -- when the whole-solve kernel runs (linear solver, CPU semantics) -- the sweep
-// that is predicted to be a frame's last one (the previous frame's iteration count) back-projects the NEXT frame's
-// measurement: that sweep evaluates the frame's final iterate anyway, and its forward projection is, up to the ratio
-// of the two normalisations, the next frame's first one. A frame that stops as predicted therefore hands the next
-// frame its first update and saves it one pass over the matrix (2 instead of 3 for a frame that needs two iterations);
-// a frame that does not stop there repeats that sweep with its own measurement (one pass lost).
+// that is predicted to be a frame's last one back-projects the NEXT frame's measurement: that sweep evaluates the
+// frame's final iterate anyway, and its forward projection is, up to the ratio of the two normalisations, the next
+// frame's first one. A frame that stops as predicted therefore hands the next frame its first update and saves it one
+// pass over the matrix (2 instead of 3 for a frame that needs two iterations); a frame that does not stop there repeats
+// that sweep with its own measurement (one pass lost). What a frame leaves for the next one (handed over or not, buffer
+// flip, iteration counts for the prediction, exchange epoch) stays on the device in a SeriesCtl block, results collect
+// in device buffers, and the host enqueues the whole chunk without waiting for any frame: one synchronisation per call.
 static int solve_series_impl(sart_engine* e, int32_t nframes, const double* measurements, const double* guess, double* solutions,
-                      int32_t* status, int32_t* iterations) {
+                             int32_t* status, int32_t* iterations) {
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256), pblocks = (uint32_t)ceil_div(e->P, 256);
     const bool whole = e->fused && e->persistent && (e->cfg.nranks <= 1 || e->peer_exchange);
-    const bool speculate = whole && !e->cfg.logarithmic && e->cfg.semantics == SART_SEMANTICS_CPU &&
-                           env_int("SART_SERIES_LOOKAHEAD", 1) != 0;
-    if (speculate && !e->d_gd_next) {
-        SART_TRY(dev_alloc(&e->d_gd_next, e->P));
-        SART_TRY(dev_alloc(&e->d_fs_next, 1));
-        SART_TRY(dev_alloc(&e->d_gspec, e->P));
-        SART_TRY(dev_alloc(&e->d_spec_scale, 1));
-    }
+    const bool chained = whole && !e->cfg.logarithmic && e->cfg.semantics == SART_SEMANTICS_CPU &&
+                         env_int("SART_SERIES_LOOKAHEAD", 1) != 0;
     e->launches = 0;
     CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
     uint64_t h2d = 0, d2h = 0;
-    int total_sweeps = 0, total_fused = 0, handed_frames = 0, repeated = 0;
-    if (nframes > 0) {
-        CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurements, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
-        h2d += e->P * sizeof(double);
-        if (guess) {
-            CUDA_TRY(cudaMemcpyAsync(e->d_xio, guess, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
-            h2d += e->V * sizeof(double);
-        }
+    if (nframes > 0 && guess) {
+        CUDA_TRY(cudaMemcpyAsync(e->d_xio, guess, e->V * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+        h2d += e->V * sizeof(double);
     }
-    bool handed = false;
-    int it_prev = -1, it_prev2 = -1, pflip_next = 0;
-    for (int32_t f = 0; f < nframes; ++f) {
-        const int has_guess = (f > 0 || guess) ? 1 : 0;
-        const bool more = f + 1 < nframes;
-        if (!speculate) {
-            if (f > 0) {
-                CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurements + (uint64_t)f * e->P, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
-                h2d += e->P * sizeof(double);
-            }
-            SART_TRY(run_solve(e, has_guess));
+
+    if (!chained) {  // the plain frame loop
+        int total_sweeps = 0, total_fused = 0;
+        for (int32_t f = 0; f < nframes; ++f) {
+            CUDA_TRY(cudaMemcpyAsync(e->d_gd, measurements + (uint64_t)f * e->P, e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+            h2d += e->P * sizeof(double);
+            SART_TRY(run_solve(e, (f > 0 || guess) ? 1 : 0));
             // passes over the matrix: set-up + one per iterate with the fused sweep, two per iteration without
             const int it = e->stats.iterations;
             total_sweeps += e->last_prologue_sweeps + (e->stats.sweep_mode == SART_SWEEP_FUSED ? it + 1 : 2 * it + 1);
             total_fused += e->stats.fused_launches;
-        } else {
-            SolveLaunch opt;
-            int sweeps = 0;
-            if (!handed) {
-                SART_TRY(frame_prologue(e, has_guess, &sweeps));
-            } else {
-                // the previous frame's last sweep already did this frame's first iteration; its statistics were reduced then
-                SART_TRY(launch_prepare(e, 0));
-                init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_st[0], e->d_st[1]);
-                CUDA_TRY(cudaGetLastError());
-                ++e->launches;
-                opt.t0 = 1;
-                opt.pflip = pflip_next;
-            }
-            if (more) {
-                CUDA_TRY(cudaMemcpyAsync(e->d_gd_next, measurements + (uint64_t)(f + 1) * e->P, e->P * sizeof(double),
-                                         cudaMemcpyHostToDevice, e->stream));
-                h2d += e->P * sizeof(double);
-                // predict "stops where the previous frame stopped" once two consecutive frames agreed to within two iterations
-                if (it_prev >= 2 && it_prev2 >= 2 && std::abs(it_prev - it_prev2) <= 2) {
-                    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_gd_next, e->P, e->d_fs_next);
-                    CUDA_TRY(cudaGetLastError());
-                    SART_TRY(allreduce_f64(e, &e->d_fs_next->gmax, 1, ncclMax));
-                    SART_TRY(allreduce_f64(e, &e->d_fs_next->gsq, 1, ncclSum));
-                    series_lookahead_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_gd_next, e->P, e->d_fs, e->d_fs_next, e->d_gspec,
-                                                                            e->d_spec_scale);
-                    CUDA_TRY(cudaGetLastError());
-                    e->launches += 2;
-                    opt.t_spec = it_prev;
-                }
-            }
-            CUDA_TRY(cudaEventRecord(e->ev_it0, e->stream));
-            if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][2], e->stream));
-            bool launched = false;
-            SART_TRY(launch_solve(e, &launched, opt));
-            if (!launched) return fail(SART_ERR_CUDA, "the device refused the cooperative launch of the whole-solve kernel in the middle of a series");
-            SART_TRY(finish_persistent_solve(e, sweeps, vblocks));
-            const IterState fin = e->last_fin;
-            handed = fin.pad == 1;
-            if (handed) {
-                pflip_next = ((fin.iterations + 1 + opt.pflip) & 1) ^ 1;  // so that the next frame's sweep 1 reads what was just written
-                std::swap(e->d_fs, e->d_fs_next);
-                ++handed_frames;
-            }
-            if ((int)e->last_tails > fin.iterations - opt.t0 + 1) ++repeated;  // a sweep ran twice
-            if (more) std::swap(e->d_gd, e->d_gd_next);
-            it_prev2 = it_prev;
-            it_prev = fin.iterations;
-            total_sweeps += sweeps + (int)e->last_tails;
-            total_fused += (int)e->last_tails;
+            if (status) status[f] = e->stats.status;
+            if (iterations) iterations[f] = e->stats.iterations;
+            CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)f * e->V, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+            d2h += e->V * sizeof(double) + 2 * sizeof(IterState);
         }
-        if (status) status[f] = e->stats.status;
-        if (iterations) iterations[f] = e->stats.iterations;
-        CUDA_TRY(cudaMemcpyAsync(solutions + (uint64_t)f * e->V, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
-        d2h += e->V * sizeof(double) + 2 * sizeof(IterState);
+        CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+        CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+        e->stats.sweeps = total_sweeps;
+        e->stats.fused_launches = total_fused;
+        e->stats.fp_launches = e->stats.bp_launches = 0;
+    } else {
+        if (!e->d_fs_next) {
+            SART_TRY(dev_alloc(&e->d_fs_next, 1));
+            SART_TRY(dev_alloc(&e->d_gspec, e->P));
+            SART_TRY(dev_alloc(&e->d_spec_scale, 1));
+            SART_TRY(dev_alloc(&e->d_series_ctl, 1));
+        }
+        if (nframes > e->series_capacity) {
+            if (e->d_series_in) CUDA_TRY(cudaFree(e->d_series_in));
+            if (e->d_series_out) CUDA_TRY(cudaFree(e->d_series_out));
+            if (e->d_series_res) CUDA_TRY(cudaFree(e->d_series_res));
+            e->d_series_in = e->d_series_out = nullptr;
+            e->d_series_res = nullptr;
+            e->series_capacity = 0;
+            SART_TRY(dev_alloc(&e->d_series_in, (uint64_t)nframes * e->P, false));
+            SART_TRY(dev_alloc(&e->d_series_out, (uint64_t)nframes * e->V, false));
+            SART_TRY(dev_alloc(&e->d_series_res, 2 * (uint64_t)nframes, false));
+            e->series_capacity = nframes;
+        }
+        SeriesCtl init = {};
+        init.it_prev = init.it_prev2 = -1;
+        init.epoch = e->xchg_epoch;
+        CUDA_TRY(cudaMemcpyAsync(e->d_series_ctl, &init, sizeof(init), cudaMemcpyHostToDevice, e->stream));
+        // the whole chunk of measurements in one copy: nothing the host does per frame waits for the device afterwards
+        CUDA_TRY(cudaMemcpyAsync(e->d_series_in, measurements, (uint64_t)nframes * e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
+        h2d += (uint64_t)nframes * e->P * sizeof(double);
+        int setup_sweeps = 0;
+        for (int32_t f = 0; f < nframes; ++f) {
+            const bool more = f + 1 < nframes;
+            int sweeps = 0;
+            // set-up of frame f; its starting solution is left alone on the device when frame f - 1 handed x_1 over
+            const double* gd = e->d_series_in + (uint64_t)f * e->P;
+            SART_TRY(frame_prologue(e, (f > 0 || guess) ? 1 : 0, &sweeps, e->d_series_ctl, gd));
+            setup_sweeps += sweeps;
+            if (more) {  // look-ahead: the next frame's measurement in this frame's normalisation
+                const double* gd_next = gd + e->P;
+                frame_stats_kernel<<<1, 1024, 0, e->stream>>>(gd_next, e->P, e->d_fs_next);
+                CUDA_TRY(cudaGetLastError());
+                SART_TRY(allreduce_f64(e, &e->d_fs_next->gmax, 1, ncclMax));
+                series_lookahead_kernel<<<pblocks, 256, 0, e->stream>>>(gd_next, e->P, e->d_fs, e->d_fs_next, e->d_gspec,
+                                                                        e->d_spec_scale);
+                CUDA_TRY(cudaGetLastError());
+                e->launches += 2;
+            }
+            SeriesLaunch sl;
+            sl.ctl = e->d_series_ctl;
+            sl.has_next = more ? 1 : 0;
+            sl.out_status = e->d_series_res + f;
+            sl.out_iterations = e->d_series_res + nframes + f;
+            bool launched = false;
+            SART_TRY(launch_solve(e, &launched, sl));
+            if (!launched) return fail(SART_ERR_CUDA, "the device refused the cooperative launch of the whole-solve kernel in the middle of a series");
+            finish_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_xd[0], e->d_xd[1], e->d_st[0], e->d_fs, e->d_xio, e->V);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+            CUDA_TRY(cudaMemcpyAsync(e->d_series_out + (uint64_t)f * e->V, e->d_xio, e->V * sizeof(double), cudaMemcpyDeviceToDevice, e->stream));
+        }
+        // one synchronisation for the whole chunk
+        SeriesCtl fin = {};
+        std::vector<int> res(2 * (size_t)nframes);
+        if (nframes > 0) {
+            CUDA_TRY(cudaMemcpyAsync(solutions, e->d_series_out, (uint64_t)nframes * e->V * sizeof(double), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(cudaMemcpyAsync(res.data(), e->d_series_res, res.size() * sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+        }
+        CUDA_TRY(cudaMemcpyAsync(&fin, e->d_series_ctl, sizeof(fin), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
+        CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
+        d2h += (uint64_t)nframes * (e->V * sizeof(double) + 2 * sizeof(int)) + sizeof(fin);
+        e->xchg_epoch = fin.epoch;
+        if (fin.timed_out)
+            return fail(SART_ERR_NCCL, "in-kernel barrier or peer-memory exchange timed out during the series: a CTA or a rank of the job did not arrive");
+        for (int32_t f = 0; f < nframes; ++f) {
+            if (status) status[f] = res[f];
+            if (iterations) iterations[f] = res[nframes + f];
+        }
+        e->stats.status = nframes ? res[nframes - 1] : 0;
+        e->stats.iterations = nframes ? res[2 * nframes - 1] : 0;
+        e->stats.sweeps = setup_sweeps + (int)fin.passes;
+        e->stats.fused_launches = (int)fin.passes;
+        e->stats.solve_launches = nframes;
+        e->stats.fp_launches = fin.frames_handed;
+        e->stats.bp_launches = fin.sweeps_repeated;
+        e->stats.fp_ms_avg = e->stats.bp_ms_avg = e->stats.tail_ms_avg = 0;
+        e->stats.sweep_mode = SART_SWEEP_FUSED;
+        e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE : SART_EXCHANGE_PEER;
     }
-    CUDA_TRY(cudaEventRecord(e->ev_solve1, e->stream));
-    CUDA_TRY(cudaEventSynchronize(e->ev_solve1));
     float ms = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&ms, e->ev_solve0, e->ev_solve1));
     e->stats.solve_ms = ms;
+    if (chained) e->stats.fused_ms_avg = e->stats.fused_launches ? ms / e->stats.fused_launches : 0;  // per pass, everything included
     e->stats.gpu_launches = e->launches;
     e->stats.h2d_bytes = h2d;
     e->stats.d2h_bytes = d2h;
-    e->stats.sweeps = total_sweeps;          // matrix passes actually made over the whole series
-    e->stats.fused_launches = total_fused;
-    e->stats.fp_launches = handed_frames;    // frames that received their first iteration from the previous frame
-    e->stats.bp_launches = repeated;         // sweeps run twice because a frame did not stop where predicted
-    e->measurement_staged = nframes > 0;
+    if (!chained) e->measurement_staged = nframes > 0;
     e->guess_staged = nframes > 0;
     return SART_OK;
 }

@@ -167,15 +167,20 @@ struct SolveArgs {
     unsigned long long epoch0;  // sweep t uses epoch0 + t + 1
     uint64_t buf_off[2];   // byte offsets of the two exchange buffers inside a region
     uint64_t flag_off;     // byte offset of the per-CTA flags [nranks][gridDim.x] inside a region
-    // Warm-started series (sart_solve_series): sweep t0 is the first one (1 when the previous frame's last sweep already
-    // produced this frame's first update), buffers are indexed by (t + pflip) & 1, and at sweep t_spec (-1: never) the
-    // back projection uses g_spec -- the NEXT frame's measurement in this frame's normalisation -- instead of g: if the
-    // solve stops there, as predicted, that sweep has at the same time evaluated this frame's last iterate and done the
-    // next frame's first iteration (out_scale converts it to the next frame's normalisation); if it does not stop, the
-    // sweep is run again with this frame's own measurement.
-    int t0, pflip, t_spec;
+    // Warm-started series (sart_solve_series), series != null: the launch takes its first sweep (1 when the previous
+    // frame's last sweep already produced this frame's first update), the buffer flip (buffers are indexed by
+    // (t + pflip) & 1) and the exchange epoch from the control block the previous frame left, and predicts its own last
+    // sweep t_spec (the previous frame's iteration count, once two consecutive frames agreed to within two iterations, and
+    // only when a next frame exists). At sweep t_spec the back projection uses g_spec -- the NEXT frame's measurement in
+    // this frame's normalisation -- instead of g: if the solve stops there, as predicted, that sweep has at the same time
+    // evaluated this frame's last iterate and done the next frame's first iteration (*out_scale converts it to the next
+    // frame's normalisation); if it does not stop, the sweep is run again with this frame's own measurement.
+    SeriesCtl* series;
+    int has_next;
     const float* g_spec;
     const double* out_scale;  // device scalar: this frame's norm / the next frame's norm
+    int* out_status;          // this frame's slots in the series' result arrays (device), or null
+    int* out_iterations;
     unsigned long long* exchanges;  // number of tails run (= exchanges over the ranks), written at the end
     unsigned long long* tail_ns;  // [3], zero at launch: ns CTA 0 spent between the end of a sweep (first grid barrier passed) and the start of the next, how often, scratch
 };
@@ -283,14 +288,24 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0, fin_stage = 0, fin_slot = 0, fin_parity = 0;  // consumers
     unsigned long long bar_target = 0;
 
-    int t_spec = -1, pflip = 0;
+    int t_spec = -1, pflip = 0, t_first = 0;
     bool repeated = false;
-    unsigned long long tails = 0;
+    unsigned long long tails = 0, epoch0 = 0;
+    SeriesCtl ctl = {};
     if constexpr (PERSIST) {
-        t_spec = sv->t_spec;
-        pflip = sv->pflip;
+        epoch0 = sv->epoch0;
+        if (sv->series) {  // every CTA reads the block long before CTA 0 rewrites it at the end of the solve
+            ctl = *sv->series;
+            epoch0 = ctl.epoch;
+            if (ctl.handed) {
+                t_first = 1;
+                pflip = ctl.pflip;
+            }
+            const int d = ctl.it_prev - ctl.it_prev2;
+            if (sv->has_next && ctl.it_prev >= 2 && ctl.it_prev2 >= 2 && d >= -2 && d <= 2) t_spec = ctl.it_prev;
+        }
     }
-    for (int t = PERSIST ? sv->t0 : 0;; ++t) {
+    for (int t = t_first;; ++t) {
         const float* xcur = a.x;
         const float* gsrc = a.g;
         if constexpr (PERSIST) {
@@ -480,7 +495,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 if (lane == 0) s_f2 = f;
             }
             const bool multi = sv->nranks > 1;
-            const unsigned long long epoch = sv->epoch0 + (++tails);  // one exchange per tail, repeated sweeps included
+            const unsigned long long epoch = epoch0 + (++tails);  // one exchange per tail, repeated sweeps included
             const uint64_t rec = (uint64_t)blk * (chunk + 1);  // this CTA's record in an exchange buffer: [sum(fit^2)][chunk]
             if (ok && multi) {
                 double* mine = reinterpret_cast<double*>(sv->peers[sv->rank] + sv->buf_off[epoch & 1]) + rec;
@@ -547,6 +562,21 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 *sv->st[0] = o;
                 *sv->st[1] = o;
                 *sv->exchanges = tails;
+                if (sv->series) {
+                    SeriesCtl c = ctl;
+                    c.handed = hand_over ? 1 : 0;
+                    c.pflip = ((t + 1 + pflip) & 1) ^ 1;  // the next launch's sweep 1 reads what the hand-over writes
+                    c.it_prev2 = ctl.it_prev;
+                    c.it_prev = t;
+                    c.epoch = epoch0 + tails;
+                    c.passes = ctl.passes + tails;
+                    c.frames_handed = ctl.frames_handed + (hand_over ? 1 : 0);
+                    c.sweeps_repeated = ctl.sweeps_repeated + ((int)tails > t - t_first + 1 ? 1 : 0);
+                    c.timed_out = ctl.timed_out | (ok ? 0 : 1);
+                    *sv->series = c;
+                    if (sv->out_status) *sv->out_status = status;
+                    if (sv->out_iterations) *sv->out_iterations = t;
+                }
             }
             if (stop && !hand_over) break;
             if (!redo) {
@@ -582,6 +612,10 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     *sv->st[0] = o;
                     *sv->st[1] = o;
                     *sv->exchanges = tails;
+                    if (sv->series) {
+                        sv->series->timed_out = 1;
+                        if (sv->out_status) *sv->out_status = kStatusExchangeTimeout;
+                    }
                 }
                 break;
             }

@@ -32,6 +32,19 @@ struct IterState {
     int pad;
 };
 
+// What one frame of a warm-started series leaves for the next one (sart_solve_series): read by the next launch of the
+// whole-solve kernel and by its set-up kernels, so that the host can enqueue a whole chunk of frames without waiting
+// for any of them.
+struct SeriesCtl {
+    int handed;              // 1: the previous frame's last sweep already did this frame's first iteration
+    int pflip;               // solution-buffer flip of the next launch when handed
+    int it_prev, it_prev2;   // iteration counts of the last two frames (-1: none yet)
+    unsigned long long epoch;  // exchange epoch after the last launch (several ranks)
+    unsigned long long passes; // sweeps run so far in this series
+    int frames_handed, sweeps_repeated;
+    int timed_out, pad;
+};
+
 struct FrameScalars {
     double gmax;  // max_i g_i over all ranks (sartsolver_cuda.cpp:147-149)
     double gsq;   // sum over g_i > 0 of g_i^2 over all ranks (sartsolver.cpp:161-164)
@@ -758,7 +771,8 @@ __global__ void series_lookahead_kernel(const double* __restrict__ g_next, uint6
 __global__ void start_solution_kernel(const double* __restrict__ sred, const double* __restrict__ xio,
                                       const double* __restrict__ ray_density, double h_d, const FrameScalars* fs,
                                       double floor_norm, double floor_orig, int from_guess, double* __restrict__ xd,
-                                      float* __restrict__ xf, uint64_t V) {
+                                      float* __restrict__ xf, uint64_t V, const SeriesCtl* series = nullptr) {
+    if (series && series->handed) return;  // the previous frame of the series has already produced this frame's x_1
     const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= V) return;
     double x;
