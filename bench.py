@@ -7,8 +7,11 @@
 Workload (all N): BASELINE.json configs[1] / configs[3]'s matrix -- synthetic 200 000 pixel x 50 000 voxel fp32
 ray-transfer matrix (40 GB) with Laplacian regularisation, row-sharded over the N GPUs exactly as the reference
 shards it over MPI ranks (strong scaling: the matrix is fixed, every GPU holds 1/N of its rows).
-A step = one frame solved with a warm start and a fixed number of iterations (--iterations, default 10): 11 forward
-and 10 back projections of the shard, the per-iteration reductions, updates and the on-device decision.
+A step = one frame solved with a warm start and a fixed number of iterations (--iterations, default 10): 11 sweeps of
+the shard (each iterate needs its forward projection; all but the last also the back projection), the per-iteration
+reductions over clusters and ranks, the updates and the on-device decisions -- by default all inside ONE cooperative
+launch of fused_solve_kernel per step, which is what the roofline entry then times (`sweeps_per_launch` sweeps of
+algorithmic bytes over the launch's CUDA-event duration).
   value  iterations/s with the frame and the starting solution already in HBM (sart_solve_resident), device time
          from CUDA events on the engine's stream, max over ranks.
   e2e    the same through sart_solve with pinned HOST buffers: the frame and the guess go up, the solution comes
