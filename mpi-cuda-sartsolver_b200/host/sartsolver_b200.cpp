@@ -105,6 +105,39 @@ int SARTSolverB200::solve(std::vector<double>& solution, const std::vector<doubl
     return status;
 }
 
+namespace {
+std::size_t frames_in(const std::vector<double>& frames, std::size_t npix) {
+    if (npix == 0 || frames.size() % npix != 0) {
+        std::cerr << "Frames vector must contain a whole number of this rank's npixel-element frames." << std::endl;
+        std::exit(1);
+    }
+    return frames.size() / npix;
+}
+}  // namespace
+
+std::vector<int> SARTSolverB200::solve_series(std::vector<double>& solution, const std::vector<double>& frames,
+                                              std::vector<double>& solutions) const {
+    if (!solution.empty() && solution.size() != nvox) {  // source/sartsolver_cuda.cpp:209-212
+        std::cerr << "Solution vector must be empty or contain nvoxel elements." << std::endl;
+        std::exit(1);
+    }
+    const std::size_t n = frames_in(frames, npix);
+    solutions.resize(n * nvox);
+    std::vector<std::int32_t> status(n, 0);
+    must(sart_solve_series(engine, (std::int32_t)n, frames.data(), solution.empty() ? nullptr : solution.data(),
+                           solutions.data(), status.data(), nullptr));
+    if (n) solution.assign(solutions.end() - (std::ptrdiff_t)nvox, solutions.end());
+    return std::vector<int>(status.begin(), status.end());
+}
+
+std::vector<int> SARTSolverB200::solve_independent(const std::vector<double>& frames, std::vector<double>& solutions) const {
+    const std::size_t n = frames_in(frames, npix);
+    solutions.resize(n * nvox);
+    std::vector<std::int32_t> status(n, 0);
+    must(sart_solve_batch(engine, (std::int32_t)n, frames.data(), solutions.data(), status.data(), nullptr));
+    return std::vector<int>(status.begin(), status.end());
+}
+
 sart_stats SARTSolverB200::last_stats() const {
     sart_stats s;
     must(sart_get_stats(engine, &s));

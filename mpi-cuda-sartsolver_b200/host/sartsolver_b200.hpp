@@ -67,6 +67,16 @@ public:
 
     int solve(std::vector<double>& solution, const std::vector<double>& measurement) const;
 
+    // Not in the reference: a cached chunk of frames in one call (the loop around solve(), source/main.cpp:125-140).
+    // frames = [n][npixel_local] row-major, solutions = [n][nvoxel] (resized); returns the n status codes.
+    //   solve_series: frame k starts from the solution of frame k - 1; `solution` is the start of frame 0 (empty = default
+    //                 initial guess) and holds the last frame's solution on return, as after n calls of solve().
+    //   solve_independent: no frame starts from another one (--no_guess).
+    // Same answers as solve() frame by frame within the parity tolerance, fewer passes over the matrix.
+    std::vector<int> solve_series(std::vector<double>& solution, const std::vector<double>& frames,
+                                  std::vector<double>& solutions) const;
+    std::vector<int> solve_independent(const std::vector<double>& frames, std::vector<double>& solutions) const;
+
     // not in the reference: what the last solve did (iterations, device times, bytes moved)
     sart_stats last_stats() const;
     std::size_t nvoxel() const { return nvox; }
