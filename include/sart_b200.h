@@ -103,6 +103,11 @@ typedef struct sart_stats {
     int32_t exchange_mode;   /* SART_EXCHANGE_*: how the per-iteration reduction over the ranks travels */
     int32_t solve_launches;  /* 1: all sweeps of the solve ran inside ONE cooperative launch (fused_solve_kernel), 0: a launch per sweep */
     double tail_ms_avg;      /* fused sweep: mean device time between two sweeps (reduction over clusters and ranks, decision, update) */
+    int32_t fused_cluster_size;  /* CTAs per thread-block cluster of the fused sweep (0: two-kernel sweep) */
+    int32_t fused_cluster_count; /* clusters resident at once = its grid / cluster size */
+    double tail_phase_us[5]; /* whole-solve kernel, mean per sweep as CTA 0 saw it: wait at the first grid barrier (the
+                                slowest cluster finishing its rows), sum over the clusters' partials, flag round trip
+                                with the other ranks, peer reads + update, second grid barrier */
 } sart_stats;
 
 typedef struct sart_device_info {
@@ -154,6 +159,13 @@ int sart_load_rows_file(sart_engine* e, const char* path, uint64_t file_offset, 
 /* Test/bench helpers without a reference counterpart: counter-based synthetic matrix keyed by GLOBAL row and
  * column (shard-invariant), and read-back of shard rows (dst leading dimension nvoxel). */
 int sart_fill_synthetic(sart_engine* e, uint64_t seed);
+/* The same with a choice of matrix: DENSE = the fill above (every element non-zero, 1 in 64 a strong "direct" one: the
+ * reflected-radiation matrices of BASELINE configs[1..4]); LOS = one straight ray per row through the nx x nz voxel grid
+ * over a weak dense background, which conditions the problem like a real tomography set-up -- warm-started frames then
+ * take tens of iterations and converge to the emission they were projected from, which the dense kind does not. */
+#define SART_SYNTHETIC_DENSE 0
+#define SART_SYNTHETIC_LOS 1
+int sart_fill_synthetic_kind(sart_engine* e, uint64_t seed, int32_t kind);
 int sart_download_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, float* dst);
 
 /* Replaces LaplacianMatrix (source/include/laplacian.hpp:15-19) as the solver sees it: COO entries with the

@@ -21,6 +21,7 @@ SEMANTICS_CPU, SEMANTICS_GPU = 0, 1
 SWEEP_AUTO, SWEEP_SPLIT, SWEEP_FUSED = 0, 1, 2
 EXCHANGE_NONE, EXCHANGE_NCCL, EXCHANGE_PEER = 0, 1, 2
 UNIQUE_ID_BYTES = 128
+SYNTHETIC_DENSE, SYNTHETIC_LOS = 0, 1
 
 # every symbol include/sart_b200.h declares (tests check the library exports exactly these)
 SYMBOLS = [
@@ -31,7 +32,7 @@ SYMBOLS = [
     "sart_set_max_iterations", "sart_set_fixed_iterations", "sart_get_config", "sart_solve", "sart_stage_measurement",
     "sart_stage_guess", "sart_solve_resident", "sart_fetch_solution", "sart_forward_project", "sart_get_stats",
     "sart_kernel_forward", "sart_kernel_backward", "sart_back_project_noalloc", "sart_load_rows_file", "sart_solve_batch",
-    "sart_solve_series",
+    "sart_solve_series", "sart_fill_synthetic_kind",
 ]
 
 
@@ -54,6 +55,7 @@ class Stats(C.Structure):
         ("matrix_bytes", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
         ("fused_ms_avg", C.c_double), ("fused_launches", C.c_int32), ("sweep_mode", C.c_int32),
         ("exchange_mode", C.c_int32), ("solve_launches", C.c_int32), ("tail_ms_avg", C.c_double),
+        ("fused_cluster_size", C.c_int32), ("fused_cluster_count", C.c_int32), ("tail_phase_us", C.c_double * 5),
     ]
 
 
@@ -93,6 +95,7 @@ def lib():
         L.sart_comm_init.argtypes = [_vp, _vp]
         L.sart_upload_rows.argtypes = [_vp, _u64, _u64, _u64, _u64, _vp, _u64]
         L.sart_fill_synthetic.argtypes = [_vp, _u64]
+        L.sart_fill_synthetic_kind.argtypes = [_vp, _u64, _i32]
         L.sart_load_rows_file.argtypes = [_vp, C.c_char_p, _u64, _u64, _u64, _u64, _u64, _u64]
         L.sart_download_rows.argtypes = [_vp, _u64, _u64, _vp]
         L.sart_set_laplacian_coo.argtypes = [_vp, _vp, _vp, _u64]
@@ -153,7 +156,17 @@ def comm_unique_id():
     return bytes(buf)
 
 
-NOALLOC_MAX_LD = 4 << 20
+def _header_constant(name):
+    """The value include/sart_b200.h gives a `#define NAME (A [<< B])` constant: the header is the one place the
+    limit of the allocation-free entry point is written down (the library checks its own array against it)."""
+    import re
+    with open(os.path.join(os.path.dirname(_HERE), "include", "sart_b200.h")) as f:
+        m = re.search(r"#define\s+" + name + r"\s+\((\d+)u?(?:\s*<<\s*(\d+))?\)", f.read())
+    return int(m.group(1)) << int(m.group(2) or 0)
+
+
+NOALLOC_MAX_LD = _header_constant("SART_NOALLOC_MAX_LD")
+NOALLOC_SCRATCH_BYTES = _header_constant("SART_NOALLOC_SCRATCH_BYTES")
 
 
 def back_project_noalloc(d_matrix, nrows, ncols, ld, d_weights, d_out, stream=None):
@@ -211,8 +224,8 @@ class Engine:
     def load_rows_file(self, path, file_offset, file_ld, local_row0, nrows, col0, ncols):
         check(lib().sart_load_rows_file(self._h, os.fsencode(path), file_offset, file_ld, local_row0, nrows, col0, ncols))
 
-    def fill_synthetic(self, seed):
-        check(lib().sart_fill_synthetic(self._h, seed))
+    def fill_synthetic(self, seed, kind=SYNTHETIC_DENSE):
+        check(lib().sart_fill_synthetic_kind(self._h, seed, kind))
 
     def download_rows(self, local_row0=0, nrows=None):
         nrows = self.nrows - local_row0 if nrows is None else nrows

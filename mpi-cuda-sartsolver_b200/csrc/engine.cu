@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <mutex>
 #include <numeric>
 #include <string>
 #include <vector>
@@ -59,6 +60,7 @@ int fail(int code, const std::string& msg) {
     } while (0)
 
 constexpr int kProfiledSweeps = 64;  // sweeps per solve whose kernels are bracketed by events
+constexpr int kSolveCtlWords = 16;   // control words of the whole-solve kernel (barrier counter, timers, counters)
 constexpr int kBpThreads = 256;
 constexpr int kFpThreads = 256;
 
@@ -68,6 +70,23 @@ int env_int(const char* name, int dflt) {
 }
 
 inline uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+// True when a CUDA profiler / tools library has been injected into this process (Nsight Compute, Nsight Systems,
+// compute-sanitizer: they all come in through CUDA_INJECTION64_PATH or leave NV_COMPUTE_PROFILER_* / NV_NSIGHT_* /
+// NSYS_* variables in the environment of the process they launch). Looked up once.
+bool profiler_attached() {
+    static const bool attached = [] {
+        const int forced = env_int("SART_ASSUME_PROFILER", -1);
+        if (forced >= 0) return forced != 0;
+        static const char* const prefixes[] = {"CUDA_INJECTION64_PATH=", "CUDA_INJECTION32_PATH=", "NV_COMPUTE_PROFILER_",
+                                               "NV_NSIGHT_", "NSYS_PROFILING_SESSION_ID=", "NV_SANITIZER_", "NVTX_INJECTION64_PATH="};
+        for (char** v = environ; v && *v; ++v)
+            for (const char* p : prefixes)
+                if (std::strncmp(*v, p, std::strlen(p)) == 0) return true;
+        return false;
+    }();
+    return attached;
+}
 
 // messages of the reference's setters, source/sartsolver.cpp:63-123
 int check_params(const sart_config& c) {
@@ -120,7 +139,8 @@ struct sart_engine {
     bool persistent = false;
     void (*fs_kernel)(const sart::FusedArgs, const sart::SolveArgs) = nullptr;
     uint32_t fs_nclusters = 0;
-    unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer, [4] tails run
+    unsigned long long* d_solve_ctl = nullptr;  // [0] grid barrier counter, [1..3] tail timer, [4] tails run, [8..12] tail phases
+    unsigned long long* h_solve_ctl = nullptr;  // pinned copy of the control words after a solve
     int last_prologue_sweeps = 0;               // matrix passes of the last frame's set-up (initial guess, log "obs")
     // warm-started series (sart_solve_series): look-ahead buffers for the next frame, allocated on first use
     double* d_series_in = nullptr;    // [capacity][P] the chunk's measurements, uploaded once
@@ -270,57 +290,50 @@ SolveKernel pick_solve_kernel(int k, int depth) {
     else if (k <= K) return depth == 3 ? fused_solve_kernel<kFusedThreads, K, 3> : fused_solve_kernel<kFusedThreads, K, 1>;
     else return pick_solve_kernel<K + 1>(k, depth);
 }
-// Geometry of the fused sweep: the smallest cluster whose CTAs can each keep their column panel of x and s in
-// registers (<= K float4 per thread), as many shared-memory stages of one row panel as fit, and as many clusters as
-// the device can keep resident. Leaves e->fused false when the shape or the device cannot run it.
-int plan_fused(sart_engine* e) {
-    e->fused = false;
-    const int mode = e->cfg.sweep_mode;
-    if (mode == SART_SWEEP_SPLIT) return SART_OK;
-    const uint32_t nt = kFusedThreads;
-    const uint64_t max_wc = (uint64_t)nt * kFusedKMax;
-    uint32_t C = 0;
-    for (uint32_t c : {1u, 2u, 4u, 8u, 16u})
-        if (ceil_div(e->ld4, c) <= max_wc) {
-            C = c;
-            break;
-        }
-    const int forced_c = env_int("SART_FUSED_CLUSTER", 0);
-    if (forced_c > 0 && ceil_div(e->ld4, (uint64_t)forced_c) <= max_wc) C = (uint32_t)forced_c;
-    auto unavailable = [&](const std::string& why) {
-        if (mode == SART_SWEEP_FUSED) return fail(SART_ERR_INVALID_ARGUMENT, "SART_SWEEP_FUSED is not available: " + why);
-        return (int)SART_OK;
-    };
-    if (!C) return unavailable("nvoxel exceeds what 16 CTAs can hold in registers");
-    const uint32_t wc = (uint32_t)ceil_div(e->ld4, C);
-    const int k_need = (int)ceil_div(wc, nt);
+// Geometry of the fused sweep. A cluster of C CTAs splits a row into C column panels; each CTA keeps its panel of x and
+// s in registers (<= K float4 per thread) and as many shared-memory stages of one row panel as fit. Every cluster size
+// from the smallest that can hold the row up to 16 is a candidate -- not only powers of two: how many clusters of C
+// the device keeps resident depends on how C packs into its GPCs (148 SMs in GPCs of 16/18/20: clusters of 4 use 132
+// SMs, of 16 only 112), so the plan asks cudaOccupancyMaxActiveClusters for each candidate, for the sweep kernel and
+// the whole-solve kernel alike, and takes the one that keeps the most SMs streaming (ties: the smaller cluster, whose
+// rows need fewer exchange messages). SART_FUSED_CLUSTER forces a size. The choice depends on the shape and the
+// device model only, so every rank of a job plans the same grid.
+// Leaves e->fused false when the shape or the device cannot run it.
+struct FusedCandidate {
+    uint32_t C = 0, wc = 0, S = 0, stage_bytes = 0, smem = 0;
+    int k = 0, nclusters = 0, nclusters_solve = 0;
+    FusedKernel fk = nullptr;
+    SolveKernel sk = nullptr;
+    std::string why;  // set when the candidate cannot run
+};
+
+FusedCandidate probe_fused(sart_engine* e, uint32_t C, int max_smem) {
+    FusedCandidate c;
+    c.C = C;
+    const uint32_t nt = kFusedThreads, nw = nt / 32, extra_warps = 2;  // + producer + reducer
+    c.wc = (uint32_t)ceil_div(e->ld4, C);
+    c.k = (int)ceil_div(c.wc, nt);
     // a stage holds K x NT float4 per row panel: the kernel reads all of it and zero-fills what the copy leaves out
-    const uint32_t stage_bytes = (uint32_t)k_need * nt * 16;
-    const uint32_t nw = nt / 32;
-    const uint32_t extra_warps = 2;  // producer + reducer
-    int max_smem = 0;
-    CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
-    uint32_t S = 0, smem = 0;
+    c.stage_bytes = (uint32_t)c.k * nt * 16;
     const uint32_t s_cap = (uint32_t)std::max(2, env_int("SART_FUSED_STAGES", 8));
     for (uint32_t s = s_cap; s >= 2; --s) {
         // stages + warp partials [2S][NWC] + per-CTA sums [2S][16] + barriers full[S], empty[S], wbar[2S], dot[2S]
-        const uint64_t need = (uint64_t)s * stage_bytes + (uint64_t)2 * s * nw * 4 + (uint64_t)2 * s * 16 * 4 + (uint64_t)6 * s * 8;
+        const uint64_t need = (uint64_t)s * c.stage_bytes + (uint64_t)2 * s * nw * 4 + (uint64_t)2 * s * 16 * 4 + (uint64_t)6 * s * 8;
         if (need + 256 <= (uint64_t)max_smem) {  // + the kernel's static shared variables
-            S = s;
-            smem = (uint32_t)need;
+            c.S = s;
+            c.smem = (uint32_t)need;
             break;
         }
     }
-    if (!S) return unavailable("a row panel does not fit twice into shared memory");
-    // long rows only, unless forced: short rows make the per-row exchange dominate
-    if (mode == SART_SWEEP_AUTO && wc < (uint32_t)env_int("SART_FUSED_MIN_WC", 1024)) return SART_OK;
-
-    const FusedKernel kFusedKernel = pick_fused_kernel<1>(k_need, fused_depth(S));
-    if (!kFusedKernel) return unavailable("no kernel instance for this panel width");
-    e->fu_kernel = kFusedKernel;
-    e->fu_threads = nt + 32 * extra_warps;
-    CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (C > 8) CUDA_TRY(cudaFuncSetAttribute(kFusedKernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    if (!c.S) {
+        c.why = "a row panel does not fit twice into shared memory";
+        return c;
+    }
+    c.fk = pick_fused_kernel<1>(c.k, fused_depth(c.S));
+    if (!c.fk) {
+        c.why = "no kernel instance for this panel width";
+        return c;
+    }
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -329,42 +342,106 @@ int plan_fused(sart_engine* e) {
     attr[0].val.clusterDim.z = 1;
     cfg.gridDim = dim3(C * (uint32_t)e->sm_count, 1, 1);
     cfg.blockDim = dim3(nt + 32 * extra_warps, 1, 1);
-    cfg.dynamicSmemBytes = smem;
+    cfg.dynamicSmemBytes = c.smem;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    int nclusters = 0;
-    cudaError_t err = cudaOccupancyMaxActiveClusters(&nclusters, kFusedKernel, &cfg);
-    if (err != cudaSuccess || nclusters <= 0) {
+    cudaError_t err = cudaFuncSetAttribute(c.fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem);
+    if (err == cudaSuccess && C > 8) err = cudaFuncSetAttribute(c.fk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (err == cudaSuccess) err = cudaOccupancyMaxActiveClusters(&c.nclusters, c.fk, &cfg);
+    if (err != cudaSuccess || c.nclusters <= 0) {
         (void)cudaGetLastError();
-        return unavailable(std::string("the device cannot co-schedule a cluster of ") + std::to_string(C) + " CTAs (" +
-                           (err != cudaSuccess ? cudaGetErrorString(err) : "0 active clusters") + ")");
+        c.why = std::string("the device cannot co-schedule a cluster of ") + std::to_string(C) + " CTAs (" +
+                (err != cudaSuccess ? cudaGetErrorString(err) : "0 active clusters") + ")";
+        c.nclusters = 0;
+        return c;
     }
+    // the whole-solve kernel needs more registers for its tail: on narrow panels fewer of its CTAs fit an SM
+    c.sk = pick_solve_kernel<1>(c.k, fused_depth(c.S));
+    if (c.sk && cudaFuncSetAttribute(c.sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)c.smem) == cudaSuccess &&
+        (C <= 8 || cudaFuncSetAttribute(c.sk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
+        cudaOccupancyMaxActiveClusters(&c.nclusters_solve, c.sk, &cfg) == cudaSuccess && c.nclusters_solve > 0) {
+        // both kernels run the smaller grid: same clusters, same partial sums, bit-identical results
+    } else {
+        c.sk = nullptr;
+        c.nclusters_solve = 0;
+    }
+    (void)cudaGetLastError();
+    return c;
+}
+
+int plan_fused(sart_engine* e) {
+    e->fused = false;
+    const int mode = e->cfg.sweep_mode;
+    if (mode == SART_SWEEP_SPLIT) return SART_OK;
+    const uint64_t max_wc = (uint64_t)kFusedThreads * kFusedKMax;
+    const uint32_t kMaxCluster = 16;
+    auto unavailable = [&](const std::string& why) {
+        if (mode == SART_SWEEP_FUSED) return fail(SART_ERR_INVALID_ARGUMENT, "SART_SWEEP_FUSED is not available: " + why);
+        return (int)SART_OK;
+    };
+    const uint64_t c_need = ceil_div(e->ld4, max_wc);
+    if (c_need > kMaxCluster) return unavailable("nvoxel exceeds what 16 CTAs can hold in registers");
+    const uint32_t c_min = (uint32_t)c_need;
+    // long rows only, unless forced: short rows make the per-row exchange dominate
+    const uint32_t min_wc = (uint32_t)env_int("SART_FUSED_MIN_WC", 1024);
+    if (mode == SART_SWEEP_AUTO && ceil_div(e->ld4, c_min) < min_wc) return SART_OK;
+    int max_smem = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+
+    const int forced_c = env_int("SART_FUSED_CLUSTER", 0);
+    FusedCandidate best;
+    std::string first_reason;
+    auto sms_used = [&](const FusedCandidate& c) {
+        const int n = c.nclusters_solve > 0 ? std::min(c.nclusters, c.nclusters_solve) : c.nclusters;
+        return (uint64_t)c.C * std::min<uint64_t>((uint64_t)n, e->P);
+    };
+    if (forced_c > 0 && (uint32_t)forced_c >= c_min && (uint32_t)forced_c <= kMaxCluster) {
+        best = probe_fused(e, (uint32_t)forced_c, max_smem);
+        first_reason = best.why;
+    } else {
+        // panels narrower than half the widest one (or than the short-row limit) are not worth their exchange traffic
+        const uint32_t c_max = std::min<uint32_t>(kMaxCluster, std::max(c_min, 2 * c_min - 1));
+        for (uint32_t C = c_min; C <= c_max; ++C) {
+            if (C > c_min && ceil_div(e->ld4, C) < min_wc) break;
+            FusedCandidate c = probe_fused(e, C, max_smem);
+            if (!c.nclusters) {
+                if (first_reason.empty()) first_reason = c.why;
+                continue;
+            }
+            if (!best.nclusters || sms_used(c) > sms_used(best)) best = c;
+        }
+    }
+    if (!best.nclusters) return unavailable(first_reason.empty() ? "no cluster size fits this shape" : first_reason);
+
+    // the probes of other candidates may have left another shared-memory size on the same kernel instance
+    CUDA_TRY(cudaFuncSetAttribute(best.fk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem));
+    if (best.sk) CUDA_TRY(cudaFuncSetAttribute(best.sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem));
+    int nclusters = best.nclusters;
     const int forced_n = env_int("SART_FUSED_CLUSTERS", 0);
     if (forced_n > 0) nclusters = std::min(nclusters, forced_n);
-    e->fu_cluster = C;
-    e->fu_wc = wc;
-    e->fu_stages = S;
-    e->fu_stage_bytes = stage_bytes;
-    e->fu_smem = smem;
+    e->fu_kernel = best.fk;
+    e->fu_threads = kFusedThreads + 64;
+    e->fu_cluster = best.C;
+    e->fu_wc = best.wc;
+    e->fu_stages = best.S;
+    e->fu_stage_bytes = best.stage_bytes;
+    e->fu_smem = best.smem;
     e->fu_nclusters = (uint32_t)std::min<uint64_t>((uint64_t)nclusters, e->P);
     e->fused = true;
 
-    // Whole solve in one cooperative launch (fused_solve_kernel), when the device can co-schedule its grid. Its tail needs
-    // more registers than the bare sweep, so on narrow panels fewer of its CTAs fit an SM; both kernels then run the
-    // smaller grid, which keeps the two ways of running a solve bit-identical (same clusters, same partial sums).
+    // Whole solve in one cooperative launch (fused_solve_kernel), when the device can co-schedule its grid.
     e->persistent = false;
     int coop = 0;
     CUDA_TRY(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, e->device));
-    const SolveKernel sk = pick_solve_kernel<1>(k_need, fused_depth(S));
-    int ncl2 = 0;
-    if (sk && cudaFuncSetAttribute(sk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
-        (C <= 8 || cudaFuncSetAttribute(sk, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
-        cudaOccupancyMaxActiveClusters(&ncl2, sk, &cfg) == cudaSuccess && ncl2 > 0) {
-        e->fu_nclusters = std::min(e->fu_nclusters, (uint32_t)ncl2);
-        e->fs_kernel = sk;
+    if (best.sk) {
+        e->fu_nclusters = std::min(e->fu_nclusters, (uint32_t)best.nclusters_solve);
+        e->fs_kernel = best.sk;
         e->fs_nclusters = e->fu_nclusters;
         e->persistent = coop && env_int("SART_PERSISTENT", 1) != 0;
-        if (e->persistent && !e->d_solve_ctl) SART_TRY(dev_alloc(&e->d_solve_ctl, 8));
+        if (e->persistent && !e->d_solve_ctl) {
+            SART_TRY(dev_alloc(&e->d_solve_ctl, kSolveCtlWords));
+            CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_solve_ctl), kSolveCtlWords * sizeof(unsigned long long)));
+        }
     }
     (void)cudaGetLastError();
     return SART_OK;
@@ -479,6 +556,7 @@ UpdArgs make_update_args(sart_engine* e, int t, const IterState* st) {
     u.eps_norm = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 1.e-7 : 0.0;
     u.eps_orig = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 0.0 : 1.e-100;
     u.log_mode = e->cfg.logarithmic;
+    u.log_caller_units = (e->cfg.semantics == SART_SEMANTICS_GPU) ? 0 : 1;
     u.out_scale = 1.0;
     return u;
 }
@@ -565,7 +643,10 @@ int launch_solve(sart_engine* e, bool* launched, const SeriesLaunch& series = Se
     sv.g_spec = e->d_gspec;
     sv.out_scale = e->d_spec_scale;
     sv.exchanges = e->d_solve_ctl + 4;
-    CUDA_TRY(cudaMemsetAsync(e->d_solve_ctl, 0, 8 * sizeof(unsigned long long), e->stream));
+    sv.phase_ns = e->d_solve_ctl + 8;
+    static_assert(8 + kTailPhases <= kSolveCtlWords, "control words");
+    sv.prefetch = env_int("SART_PREFETCH", 1) != 0 ? 1 : 0;
+    CUDA_TRY(cudaMemsetAsync(e->d_solve_ctl, 0, kSolveCtlWords * sizeof(unsigned long long), e->stream));
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -579,18 +660,27 @@ int launch_solve(sart_engine* e, bool* launched, const SeriesLaunch& series = Se
     cfg.dynamicSmemBytes = e->fu_smem;
     cfg.stream = e->stream;
     cfg.attrs = attr;
-    // SART_COOPERATIVE=0 drops the cooperative attribute (Nsight Compute 2025.2 cannot replay a cooperative cluster
-    // launch: "LaunchFailed"). The grid is the same and still fits the device at once (cudaOccupancyMaxActiveClusters),
-    // but then nothing checks that the GPU is not shared; a CTA that never becomes resident ends the solve through
-    // the barrier timeout instead of a launch error.
-    cfg.numAttrs = env_int("SART_COOPERATIVE", 1) != 0 ? 2 : 1;
-    const cudaError_t err = cudaLaunchKernelEx(&cfg, e->fs_kernel, a, sv);
-    if (err == cudaErrorCooperativeLaunchTooLarge || err == cudaErrorNotSupported || err == cudaErrorInvalidValue ||
-        err == cudaErrorInvalidConfiguration) {
+    // Without the cooperative attribute the grid is the same and still fits the device at once
+    // (cudaOccupancyMaxActiveClusters), but nothing checks that the GPU is not shared; a CTA that never becomes
+    // resident ends the solve through the barrier timeout instead of a launch error. The attribute is dropped
+    //   * on request (SART_COOPERATIVE=0),
+    //   * when a profiler has injected itself into the process (Nsight Compute 2025.2 cannot replay a cooperative
+    //     cluster launch: "LaunchFailed", and the process dies) -- so `ncu python ...` over any caller just works,
+    //   * for a second attempt when the driver refuses the cooperative launch.
+    // If that fails as well the caller falls back to one launch per sweep.
+    const bool coop = env_int("SART_COOPERATIVE", 1) != 0 && !profiler_attached();
+    cfg.numAttrs = coop ? 2 : 1;
+    cudaError_t err = cudaLaunchKernelEx(&cfg, e->fs_kernel, a, sv);
+    if (err != cudaSuccess && coop) {
+        (void)cudaGetLastError();
+        cfg.numAttrs = 1;
+        err = cudaLaunchKernelEx(&cfg, e->fs_kernel, a, sv);
+    }
+    if (err != cudaSuccess) {
+        // not launched: nothing has run, the error is not sticky (a sticky one shows up again in the fallback path)
         (void)cudaGetLastError();
         return SART_OK;
     }
-    CUDA_TRY(err);
     ++e->launches;
     *launched = true;
     return SART_OK;
@@ -696,14 +786,13 @@ int launch_prepare(sart_engine* e, int weights_mode, const double* gd) {
 // What follows the whole-solve kernel: final state to the host, un-normalised solution, statistics.
 int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks) {
     if (e->profiling) CUDA_TRY(cudaEventRecord(e->ev_prof[0][3], e->stream));
-    unsigned long long tail[4] = {0, 0, 0, 0};  // tail time (ns), tails timed, scratch, tails run
-    static_assert(sizeof(tail) <= sizeof(IterState), "the second pinned slot carries the control words");
     CUDA_TRY(cudaMemcpyAsync(&e->h_st[0], e->d_st[0], sizeof(IterState), cudaMemcpyDeviceToHost, e->stream));
-    CUDA_TRY(cudaMemcpyAsync(&e->h_st[1], e->d_solve_ctl + 1, sizeof(tail), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(cudaMemcpyAsync(e->h_solve_ctl, e->d_solve_ctl, kSolveCtlWords * sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(cudaEventRecord(e->ev_batch[0], e->stream));
     CUDA_TRY(cudaEventSynchronize(e->ev_batch[0]));
     const IterState fin = e->h_st[0];
-    std::memcpy(tail, &e->h_st[1], sizeof(tail));
+    const unsigned long long* tail = e->h_solve_ctl + 1;  // tail time (ns), tails timed, scratch, tails run
+    const unsigned long long* phase = e->h_solve_ctl + 8;
     if (!fin.done) return fail(SART_ERR_STATE, "whole-solve kernel ended without a decision (internal error)");
     if (fin.status == kStatusExchangeTimeout)
         return fail(SART_ERR_NCCL, "in-kernel barrier or peer-memory exchange timed out: a CTA or a rank of the job did not arrive");
@@ -726,6 +815,7 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
     e->stats.fused_launches = nsweeps;
     e->stats.solve_launches = 1;
     e->stats.tail_ms_avg = tail[1] ? 1e-6 * (double)tail[0] / (double)tail[1] : 0;
+    for (int k = 0; k < kTailPhases; ++k) e->stats.tail_phase_us[k] = tail[1] ? 1e-3 * (double)phase[k] / (double)tail[1] : 0;
     e->stats.sweep_mode = SART_SWEEP_FUSED;
     e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE : SART_EXCHANGE_PEER;
     if (e->profiling) {
@@ -1274,6 +1364,7 @@ void free_engine(sart_engine* e) {
     if (e->d_xchg) cudaFree(e->d_xchg);
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
+    if (e->h_solve_ctl) cudaFreeHost(e->h_solve_ctl);
     void* series_ptrs[] = {e->d_series_in, e->d_fs_next, e->d_gspec, e->d_spec_scale, e->d_series_ctl, e->d_series_out, e->d_series_res};
     for (void* p : series_ptrs)
         if (p) cudaFree(p);
@@ -1556,17 +1647,32 @@ int sart_load_rows_file(sart_engine* e, const char* path, uint64_t file_offset, 
     return rc;
 }
 
-int sart_fill_synthetic(sart_engine* e, uint64_t seed) {
+int sart_fill_synthetic_kind(sart_engine* e, uint64_t seed, int32_t kind) {
     SART_TRY(require(e, false));
-    const int exponent = (int)std::lround(std::log2((double)e->V * 98304.0));
-    const float scale = std::ldexp(1.0f, -exponent);
     const dim3 grid((uint32_t)std::min<uint64_t>(ceil_div(e->ld4, 256), 64), (uint32_t)std::min<uint64_t>(e->P, 32768));
-    fill_synthetic_kernel<<<grid, 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, e->row_offset, seed, scale);
+    if (kind == SART_SYNTHETIC_DENSE) {
+        const int exponent = (int)std::lround(std::log2((double)e->V * 98304.0));
+        const float scale = std::ldexp(1.0f, -exponent);
+        fill_synthetic_kernel<<<grid, 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, e->row_offset, seed, scale);
+    } else if (kind == SART_SYNTHETIC_LOS) {
+        // the voxel grid nx x nz: nvoxel factored as squarely as possible (the tests' voxel_grid_shape)
+        uint64_t nx = (uint64_t)std::floor(std::sqrt((double)e->V));
+        while (nx > 1 && e->V % nx) --nx;
+        const uint64_t nz = e->V / nx;
+        // mean row sum of q: a ray crosses about 2430 sqrt(V) units of "direct" weight, plus 128 per background element
+        const int exponent = (int)std::lround(std::log2(1024.0 * 2430.0 * std::sqrt((double)e->V) + 128.0 * (double)e->V));
+        const float scale = std::ldexp(1.0f, -exponent);
+        fill_los_kernel<<<grid, 256, 0, e->stream>>>(e->dH, e->ld4, e->P, e->V, e->row_offset, seed, scale, (uint32_t)nx, (uint32_t)nz);
+    } else {
+        return fail(SART_ERR_INVALID_ARGUMENT, "sart_fill_synthetic_kind: unknown kind");
+    }
     CUDA_TRY(cudaGetLastError());
     CUDA_TRY(cudaStreamSynchronize(e->stream));
     e->finalized = false;
     return SART_OK;
 }
+
+int sart_fill_synthetic(sart_engine* e, uint64_t seed) { return sart_fill_synthetic_kind(e, seed, SART_SYNTHETIC_DENSE); }
 
 int sart_download_rows(sart_engine* e, uint64_t local_row0, uint64_t nrows, float* dst) {
     SART_TRY(require(e, false));
@@ -1600,13 +1706,18 @@ int sart_finalize(sart_engine* e) {
     slabs = ceil_div(e->P, rows_per_slab);
     double* d_part = nullptr;
     SART_TRY(dev_alloc(&d_part, slabs * e->V, false));
-    col_sums_f64_kernel<<<dim3(cblocks, (uint32_t)slabs), 256, 0, e->stream>>>(e->dH, e->ld, e->P, e->V, rows_per_slab, d_part);
-    CUDA_TRY(cudaGetLastError());
-    reduce_f64_partials_kernel<<<cblocks, 256, 0, e->stream>>>(d_part, (uint32_t)slabs, e->V, e->d_rho);
-    CUDA_TRY(cudaGetLastError());
-    SART_TRY(allreduce_f64(e, e->d_rho, e->V, ncclSum));
-    CUDA_TRY(cudaStreamSynchronize(e->stream));
-    CUDA_TRY(cudaFree(d_part));
+    const int rc = [&]() -> int {  // so that the partials are freed on every way out
+        col_sums_f64_kernel<<<dim3(cblocks, (uint32_t)slabs), 256, 0, e->stream>>>(e->dH, e->ld, e->P, e->V, rows_per_slab, d_part);
+        CUDA_TRY(cudaGetLastError());
+        reduce_f64_partials_kernel<<<cblocks, 256, 0, e->stream>>>(d_part, (uint32_t)slabs, e->V, e->d_rho);
+        CUDA_TRY(cudaGetLastError());
+        SART_TRY(allreduce_f64(e, e->d_rho, e->V, ncclSum));
+        CUDA_TRY(cudaStreamSynchronize(e->stream));
+        return SART_OK;
+    }();
+    const cudaError_t free_err = cudaFree(d_part);
+    SART_TRY(rc);
+    CUDA_TRY(free_err);
     SART_TRY(build_laplacian(e));
     e->finalized = true;
     return SART_OK;
@@ -1976,6 +2087,8 @@ int sart_get_stats(const sart_engine* e, sart_stats* out) {
     if (!e || !out) return fail(SART_ERR_INVALID_ARGUMENT, "engine or out is NULL");
     *out = e->stats;
     out->matrix_bytes = e->P * e->V * 4;
+    out->fused_cluster_size = e->fused ? (int32_t)e->fu_cluster : 0;
+    out->fused_cluster_count = e->fused ? (int32_t)e->fu_nclusters : 0;
     return SART_OK;
 }
 
@@ -2005,7 +2118,9 @@ int sart_get_stats(const sart_engine* e, sart_stats* out) {
 //     first call may make the runtime load the module, so make it before any stream capture begins.
 // The function calls no cudaMalloc / cudaFree / cudaMallocAsync and no library routine that allocates on the device.
 // =====================================================================================================================
-#define SART_NOALLOC_SCRATCH_FLOATS (4u << 20)
+#define SART_NOALLOC_SCRATCH_FLOATS (SART_NOALLOC_SCRATCH_BYTES / sizeof(float))
+static_assert(SART_NOALLOC_SCRATCH_FLOATS == SART_NOALLOC_MAX_LD,
+              "the documented limit (SART_NOALLOC_MAX_LD) is one row of partials in the built-in array");
 
 static __device__ __align__(256) float g_noalloc_scratch[SART_NOALLOC_SCRATCH_FLOATS];
 

@@ -183,7 +183,13 @@ struct SolveArgs {
     int* out_iterations;
     unsigned long long* exchanges;  // number of tails run (= exchanges over the ranks), written at the end
     unsigned long long* tail_ns;  // [3], zero at launch: ns CTA 0 spent between the end of a sweep (first grid barrier passed) and the start of the next, how often, scratch
+    // [kTailPhases], zero at launch: ns CTA 0 spent in each part of the tails (summed over the tails tail_ns[1] counts):
+    // waiting at the first grid barrier (= how much later the slowest cluster finished its rows), adding the clusters'
+    // partials, the flag round trip with the other ranks, reading the peers' records + update, the second grid barrier
+    unsigned long long* phase_ns;
+    int prefetch;  // 1: the producer warps run ahead into the next sweep while the tail is being computed
 };
+constexpr int kTailPhases = 5;
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
     unsigned long long t;
@@ -305,6 +311,11 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             if (sv->has_next && ctl.it_prev >= 2 && ctl.it_prev2 >= 2 && d >= -2 && d <= 2) t_spec = ctl.it_prev;
         }
     }
+    // Rows of the coming sweep whose copies the producer already issued while the previous tail was running: the matrix
+    // does not depend on the iterate, so the producer simply keeps going into the next sweep's first rows as the
+    // consumers release the last stages of this one, and the reduction / exchange / update between two sweeps overlaps
+    // with refilling the whole shared-memory ring (S row panels per SM) from HBM. Same on every thread (uniform inputs).
+    bool ahead_prev = false;  // the previous tail of this launch was overlapped that way
     for (int t = t_first;; ++t) {
         const float* xcur = a.x;
         const float* gsrc = a.g;
@@ -312,24 +323,37 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             xcur = sv->xf[(t + pflip) & 1];
             if (t == t_spec) gsrc = sv->g_spec;
         }
+        // another sweep can only follow while t < max_iter (the decision of sweep max_iter is always "stop"), and none
+        // is expected after the sweep a series predicts to be the frame's last
+        auto runs_ahead = [&]() {
+            if constexpr (PERSIST) return sv->prefetch && t < sv->max_iter && t != t_spec;
+            else return false;
+        };
 
         if (warp == NWC) {
             // ---- producer --------------------------------------------------------------------------------------------
             if (lane == 0) {
                 const uint32_t bytes = wcols * 16;
-                const char* src = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
+                const char* src0 = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
                 const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
-                for (uint32_t r = 0; r < n; ++r) {
+                auto issue = [&](const char* src) {
                     mbar_wait(empty_u32 + 8 * pr_stage, pr_parity);
                     mbar_expect_tx(dot_u32 + 8 * pr_slot, 4 * C);  // one float from every CTA of the cluster
                     mbar_expect_tx(full_u32 + 8 * pr_stage, bytes);
                     if (bytes) bulk_load(ring_u32 + pr_stage * a.stage_bytes, src, bytes, full_u32 + 8 * pr_stage);
-                    src += src_step;
                     if (++pr_stage == S) {
                         pr_stage = 0;
                         pr_parity ^= 1;
                     }
                     if (++pr_slot == 2 * S) pr_slot = 0;
+                };
+                const uint32_t pre = ahead_prev ? min(S, n) : 0u;
+                const char* src = src0 + (uint64_t)pre * src_step;
+                for (uint32_t r = pre; r < n; ++r, src += src_step) issue(src);
+                if constexpr (PERSIST) {
+                    const uint32_t npre = runs_ahead() ? min(S, n) : 0u;
+                    src = src0;
+                    for (uint32_t r = 0; r < npre; ++r, src += src_step) issue(src);  // the next sweep's first rows
                 }
             }
             __syncwarp();
@@ -471,9 +495,19 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
         } else {
             // ---- tail of sweep t ----------------------------------------------------------------------------------------
             const uint32_t nblk = gridDim.x, blk = blockIdx.x;
+            const bool timer = (blk == 0 && tid == 0);
+            unsigned long long tp = timer ? global_timer_ns() : 0ull;  // CTA 0 has finished its own rows
+            auto phase_done = [&](int k) {
+                if (timer) {
+                    const unsigned long long now = global_timer_ns();
+                    sv->phase_ns[k] += now - tp;
+                    tp = now;
+                }
+            };
             bar_target += nblk;
             bool ok = grid_barrier(sv->gbar, bar_target, &s_abort);
-            if (blk == 0 && tid == 0) sv->tail_ns[2] = global_timer_ns();  // the slowest cluster has finished its rows
+            if (timer) sv->tail_ns[2] = global_timer_ns();  // the slowest cluster has finished its rows
+            phase_done(0);
             const uint64_t V = sv->V, chunk = (V + nblk - 1) / nblk;
             const uint64_t j0 = min(V, (uint64_t)blk * chunk), j1 = min(V, j0 + chunk);
             // this rank's partial of voxel j: the clusters' partials in fixed order (reduce_partials_kernel)
@@ -504,6 +538,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 if (tid == 0) mine[0] = s_f2;
                 __threadfence_system();
                 __syncthreads();
+                phase_done(1);
                 if (tid < sv->nranks) {
                     const uint64_t fl = sv->flag_off + ((uint64_t)sv->rank * nblk + blk) * 8;
                     st_release_sys_u64(reinterpret_cast<unsigned long long*>(sv->peers[tid] + fl), epoch);
@@ -520,6 +555,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 }
             }
             __syncthreads();
+            if (multi) phase_done(2);
             if (s_abort) ok = false;
             // decision for x_t (decide_kernel / xchg_decide_update_kernel): identical in every CTA of every rank
             bool stop = false;
@@ -578,7 +614,25 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     if (sv->out_iterations) *sv->out_iterations = t;
                 }
             }
-            if (stop && !hand_over) break;
+            // Leaving the loop with copies of the next sweep's first rows still in flight: they must have landed before the
+            // CTA may exit (its shared memory is their destination).
+            auto drain = [&]() {
+                if (tid == 0) {
+                    uint32_t st = fp_stage, par = fp_parity;
+                    const uint32_t npre = runs_ahead() ? min(S, n) : 0u;
+                    for (uint32_t i = 0; i < npre; ++i) {
+                        mbar_wait(full_u32 + 8 * st, par);
+                        if (++st == S) {
+                            st = 0;
+                            par ^= 1;
+                        }
+                    }
+                }
+            };
+            if (stop && !hand_over) {
+                drain();
+                break;
+            }
             if (!redo) {
                 UpdArgs u = sv->upd;
                 u.xd_cur = sv->xd[(t + pflip) & 1];
@@ -588,18 +642,33 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) {
                     double sj;
                     if (multi) {
+                        // all ranks' values of this voxel requested before the first one is used: one NVLink round trip
+                        // instead of one per rank; added in rank order, so every rank gets the same bits
                         sj = 0.0;
-                        for (uint32_t r = 0; r < sv->nranks; ++r)
-                            sj += __ldcv(reinterpret_cast<const double*>(sv->peers[r] + sv->buf_off[epoch & 1]) + rec + 1 + (j - j0));
+                        for (int r0 = 0; r0 < (int)sv->nranks; r0 += 8) {  // (8 at a time: one batch on a box of 8 GPUs)
+                            double pr[8];
+#pragma unroll
+                            for (int r = 0; r < 8; ++r)
+                                if (r0 + r < (int)sv->nranks)
+                                    pr[r] = __ldcv(reinterpret_cast<const double*>(sv->peers[r0 + r] + sv->buf_off[epoch & 1]) + rec + 1 + (j - j0));
+#pragma unroll
+                            for (int r = 0; r < 8; ++r)
+                                if (r0 + r < (int)sv->nranks) sj += pr[r];
+                        }
                     } else {
                         sj = local_sum(j);
                     }
                     apply_update(u, j, sj);
                 }
             }
-            if (hand_over) break;
+            phase_done(multi ? 3 : 1);
+            if (hand_over) {
+                drain();
+                break;
+            }
             bar_target += nblk;
             if (!grid_barrier(sv->gbar, bar_target, &s_abort)) {
+                drain();
                 if (tid == 0) {
                     IterState o;
                     o.conv_prev = conv_prev;
@@ -619,10 +688,12 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 }
                 break;
             }
-            if (blk == 0 && tid == 0) {
+            phase_done(4);
+            if (timer) {
                 sv->tail_ns[0] += global_timer_ns() - sv->tail_ns[2];
                 sv->tail_ns[1] += 1;
             }
+            ahead_prev = runs_ahead();
             if (redo) {  // the partials of this sweep have been read by everyone (barrier above): run sweep t again
                 t_spec = -1;
                 repeated = true;

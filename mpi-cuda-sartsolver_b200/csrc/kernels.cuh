@@ -534,6 +534,8 @@ struct UpdArgs {
     double beta, relax, h_d;
     double eps_norm, eps_orig;  // log solver's epsilon: in normalised units (GPU semantics) or caller units (CPU, 1e-100)
     int log_mode;
+    int log_caller_units;       // log solver: the penalty takes log(x) of the solution in the caller's units (CPU solver,
+                                // sartsolver.cpp:292) instead of the normalised one (GPU solver, sart_kernels.cu:200)
     double out_scale;           // 1, or the factor into the next frame's normalisation (series hand-over, fused.cuh)
 };
 
@@ -543,9 +545,13 @@ __device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, doubl
     double pen = 0.0;
     if (a.lap_rowptr) {
         const int b = a.lap_rowptr[j], e = a.lap_rowptr[j + 1];
+        // The iterate is kept as x / max(g). The linear penalty is scale-covariant; the log solver's is not: the CPU
+        // solver takes log() of the solution in the caller's units, so a Laplacian row whose entries do not add up to
+        // zero sees the normalisation (beta * log(norm) * rowsum). The GPU solver takes it of the normalised iterate.
+        const double unit = (a.log_mode && a.log_caller_units) ? a.fs->norm : 1.0;
         for (int k = b; k < e; ++k) {
             const double xv = __ldcg(a.xd_cur + a.lap_col[k]);
-            pen += a.beta * (double)a.lap_val[k] * (a.log_mode ? log(xv) : xv);
+            pen += a.beta * (double)a.lap_val[k] * (a.log_mode ? log(xv * unit) : xv);
         }
     }
     const double rho = a.ray_density[j];
@@ -906,6 +912,55 @@ __global__ void fill_synthetic_kernel(float* __restrict__ H, uint64_t ld4, uint6
             v.y = (j + 1 < V) ? synth_element(seed, flat0 + j + 1, scale) : 0.f;
             v.z = (j + 2 < V) ? synth_element(seed, flat0 + j + 2, scale) : 0.f;
             v.w = (j + 3 < V) ? synth_element(seed, flat0 + j + 3, scale) : 0.f;
+            p[c] = v;
+        }
+    }
+}
+
+// "Line of sight" matrix (SART_SYNTHETIC_LOS): every row is one ray through the nx x nz voxel grid -- a band a few
+// voxels wide around a straight line, drawn per row from the hash of the GLOBAL row index -- over a weak dense
+// background ("reflections", 8 bits per element). Integer arithmetic only, so the CPU generator of the tests produces
+// the same bits: with (u, w) = (j / nz, j % nz) the voxel of column j,
+//     direct = max(0, 2048 - |a u + b w - c|) / 2        |a| + |b| = 1024, the line passes through a voxel (u0, w0)
+//     q      = direct * 1024 + (bg | 1)                   q < 2^21, exact in fp32
+// and H_ij = q * 2^-e. Unlike the dense kind this one behaves like a tomography problem: a warm-started frame needs
+// some ten iterations at a tolerance of 1e-6 and ends within a few per cent of the emission it was projected from.
+struct LosRay {
+    long long a, b, c;
+};
+__device__ __forceinline__ LosRay los_ray(uint64_t seed, uint64_t row, uint32_t nx, uint32_t nz) {
+    const uint64_t h = splitmix64((seed ^ 0xA5A5A5A55A5A5A5AULL) ^ (row * 0xD1342543DE82EF95ULL));
+    const uint64_t h2 = splitmix64(h);
+    LosRay r;
+    r.a = (long long)(h & 2047u) - 1023;
+    const long long mag = 1024 - (r.a < 0 ? -r.a : r.a);
+    r.b = ((h >> 11) & 1u) ? mag : -mag;
+    const long long u0 = (long long)((h2 & 0xFFFFFFu) % nx), w0 = (long long)(((h2 >> 24) & 0xFFFFFFu) % nz);
+    r.c = r.a * u0 + r.b * w0;
+    return r;
+}
+__device__ __forceinline__ float los_element(const LosRay& r, uint64_t seed, uint64_t flat, uint32_t j, uint32_t nz, float scale) {
+    const long long u = j / nz, w = j % nz;
+    long long d = r.a * u + r.b * w - r.c;
+    d = d < 0 ? -d : d;
+    const uint32_t direct = d < 2048 ? (uint32_t)(2048 - d) >> 1 : 0u;
+    const uint32_t bg = (uint32_t)(splitmix64((seed + 1) ^ (flat * 0xD1342543DE82EF95ULL)) >> 56) | 1u;
+    return (float)(direct * 1024u + bg) * scale;
+}
+
+__global__ void fill_los_kernel(float* __restrict__ H, uint64_t ld4, uint64_t P, uint64_t V, uint64_t row_offset,
+                                uint64_t seed, float scale, uint32_t nx, uint32_t nz) {
+    for (uint64_t row = blockIdx.y; row < P; row += gridDim.y) {
+        const uint64_t flat0 = (row_offset + row) * V;
+        const LosRay ray = los_ray(seed, row_offset + row, nx, nz);
+        float4* __restrict__ p = reinterpret_cast<float4*>(H) + row * ld4;
+        for (uint64_t c = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; c < ld4; c += (uint64_t)gridDim.x * blockDim.x) {
+            const uint32_t j = (uint32_t)(4 * c);
+            float4 v;
+            v.x = (j + 0 < V) ? los_element(ray, seed, flat0 + j + 0, j + 0, nz, scale) : 0.f;
+            v.y = (j + 1 < V) ? los_element(ray, seed, flat0 + j + 1, j + 1, nz, scale) : 0.f;
+            v.z = (j + 2 < V) ? los_element(ray, seed, flat0 + j + 2, j + 2, nz, scale) : 0.f;
+            v.w = (j + 3 < V) ? los_element(ray, seed, flat0 + j + 3, j + 3, nz, scale) : 0.f;
             p[c] = v;
         }
     }

@@ -60,6 +60,9 @@ class Restatement:
                                    C.POINTER(OracleParams), C.POINTER(C.c_int), C.c_void_p]
         L.oracle_solve.restype = C.c_int
         L.oracle_fill_synthetic.argtypes = [_pf, _u64, _u64, _u64, _u64]
+        L.oracle_fill_los.argtypes = [_pf, _u64, _u64, _u64, _u64]
+        L.oracle_los_exponent.argtypes = [_u64]
+        L.oracle_los_exponent.restype = C.c_int
         L.oracle_forward.argtypes = [_pf, _u64, _u64, _pd, _pd]
         L.oracle_synth_exponent.argtypes = [_u64]
         L.oracle_synth_exponent.restype = C.c_int
@@ -69,9 +72,10 @@ class Restatement:
         self.lib.oracle_shard_range(npixel, nranks, rank, C.byref(off), C.byref(n))
         return off.value, n.value
 
-    def fill_synthetic(self, npixel, nvoxel, seed, row0=0):
+    def fill_synthetic(self, npixel, nvoxel, seed, row0=0, kind=0):
+        """kind 0: the dense matrix, 1: the line-of-sight matrix (SART_SYNTHETIC_DENSE / _LOS of the product)."""
         H = np.empty((npixel, nvoxel), dtype=np.float32)
-        self.lib.oracle_fill_synthetic(H, row0, npixel, nvoxel, seed)
+        (self.lib.oracle_fill_los if kind == 1 else self.lib.oracle_fill_synthetic)(H, row0, npixel, nvoxel, seed)
         return H
 
     def forward(self, H, x):

@@ -169,7 +169,9 @@ int oracle_solve(const float* H, uint64_t npixel, uint64_t nvoxel, const uint64_
         for (uint64_t j = 0; j < nvoxel; ++j) pen[j] = 0;
         for (uint64_t k = 0; k < lap_nnz; ++k) {
             const uint64_t iv = lap_idx[k] / nvoxel, jv = lap_idx[k] % nvoxel;
-            const double s = prm->logarithmic ? log(x[jv]) : x[jv];
+            /* CPU solver: log of the solution in caller units (:292). GPU solver: __logf of the iterate it keeps
+             * divided by max(g) (sart_kernels.cu:200 on sartsolver_cuda.cpp:177's normalised vector). */
+            const double s = prm->logarithmic ? log(prm->gpu_semantics ? x[jv] / norm : x[jv]) : x[jv];
             pen[iv] += beta * (double)lap_val[k] * s;
         }
 
@@ -261,6 +263,44 @@ void oracle_fill_synthetic(float* H, uint64_t row0, uint64_t nrows, uint64_t nvo
         const uint64_t i = row0 + (uint64_t)r;
         float* row = H + (uint64_t)r * nvoxel;
         for (uint64_t j = 0; j < nvoxel; ++j) row[j] = oracle_synth_element(seed, i * nvoxel + j, e);
+    }
+}
+
+/* The "line of sight" kind of the product's generator (SART_SYNTHETIC_LOS, kernels.cuh): one straight ray per row through
+ * the nx x nz voxel grid over a weak 8-bit background, integers only. */
+void oracle_grid_shape(uint64_t nvoxel, uint64_t* nx, uint64_t* nz) {
+    uint64_t n = (uint64_t)floor(sqrt((double)nvoxel));
+    while (n > 1 && nvoxel % n) --n;
+    *nx = n;
+    *nz = nvoxel / n;
+}
+
+int oracle_los_exponent(uint64_t nvoxel) {
+    return (int)lround(log2(1024.0 * 2430.0 * sqrt((double)nvoxel) + 128.0 * (double)nvoxel));
+}
+
+void oracle_fill_los(float* H, uint64_t row0, uint64_t nrows, uint64_t nvoxel, uint64_t seed) {
+    uint64_t nx, nz;
+    oracle_grid_shape(nvoxel, &nx, &nz);
+    const int e = oracle_los_exponent(nvoxel);
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < (int64_t)nrows; ++r) {
+        const uint64_t i = row0 + (uint64_t)r;
+        const uint64_t h = oracle_splitmix64((seed ^ 0xA5A5A5A55A5A5A5AULL) ^ (i * 0xD1342543DE82EF95ULL));
+        const uint64_t h2 = oracle_splitmix64(h);
+        const int64_t a = (int64_t)(h & 2047u) - 1023;
+        const int64_t mag = 1024 - (a < 0 ? -a : a);
+        const int64_t b = ((h >> 11) & 1u) ? mag : -mag;
+        const int64_t u0 = (int64_t)((h2 & 0xFFFFFFu) % nx), w0 = (int64_t)(((h2 >> 24) & 0xFFFFFFu) % nz);
+        const int64_t c = a * u0 + b * w0;
+        float* row = H + (uint64_t)r * nvoxel;
+        for (uint64_t j = 0; j < nvoxel; ++j) {
+            int64_t d = a * (int64_t)(j / nz) + b * (int64_t)(j % nz) - c;
+            d = d < 0 ? -d : d;
+            const uint32_t direct = d < 2048 ? (uint32_t)(2048 - d) >> 1 : 0u;
+            const uint32_t bg = (uint32_t)(oracle_splitmix64((seed + 1) ^ ((i * nvoxel + j) * 0xD1342543DE82EF95ULL)) >> 56) | 1u;
+            row[j] = ldexpf((float)(direct * 1024u + bg), -e);
+        }
     }
 }
 

@@ -43,6 +43,9 @@ uint64_t oracle_splitmix64(uint64_t z);
 int oracle_synth_exponent(uint64_t nvoxel);
 float oracle_synth_element(uint64_t seed, uint64_t flat_index, int exponent);
 void oracle_fill_synthetic(float* H, uint64_t row0, uint64_t nrows, uint64_t nvoxel, uint64_t seed);
+void oracle_grid_shape(uint64_t nvoxel, uint64_t* nx, uint64_t* nz);
+int oracle_los_exponent(uint64_t nvoxel);
+void oracle_fill_los(float* H, uint64_t row0, uint64_t nrows, uint64_t nvoxel, uint64_t seed);
 void oracle_forward(const float* H, uint64_t npixel, uint64_t nvoxel, const double* x, double* out);
 
 #ifdef __cplusplus

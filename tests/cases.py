@@ -40,6 +40,14 @@ CASES = {
     "log_laplacian_np3": dict(P=320, V=144, seed=9, laplacian=True,
                               kw=dict(max_iterations=30, conv_tolerance=1e-30, logarithmic=True, relaxation=0.7,
                                       nranks=3, beta_laplace=2e-2)),
+    # Laplacian rows that do not add up to zero (a constant on the diagonal, as a boundary row with a fixed value has)
+    # and a frame far from max(g) = 1: the log solver's penalty beta * L * log(x) then depends on the units of x
+    # (source/sartsolver.cpp:292 takes the log of the solution as the caller gave it).
+    "log_laplacian_rowsum": dict(P=320, V=144, seed=19, laplacian=True, lap_diag_add=0.5, g_scale=37.5,
+                                 kw=dict(max_iterations=20, conv_tolerance=1e-30, logarithmic=True, relaxation=0.8,
+                                         beta_laplace=2e-2)),
+    "linear_laplacian_rowsum": dict(P=320, V=144, seed=20, laplacian=True, lap_diag_add=0.5, g_scale=37.5,
+                                    kw=dict(max_iterations=20, conv_tolerance=1e-30, beta_laplace=2e-2)),
     "log_tol": dict(P=256, V=96, seed=21, kw=dict(max_iterations=500, conv_tolerance=1e-5, logarithmic=True)),
     "max_iterations_exceeded": dict(P=128, V=64, seed=3, kw=dict(max_iterations=3, conv_tolerance=1e-12)),
     "series_warm4": dict(P=256, V=100, seed=13, frames=4, laplacian=True,
@@ -62,10 +70,16 @@ def build_case(name, restatement):
     nframes = c.get("frames", 1)
     frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=f / max(1, nframes - 1) if nframes > 1 else 0.0))
                        for f in range(nframes)])
+    frames = frames * c.get("g_scale", 1.0)
     if c.get("saturated_every"):
         frames[:, ::c["saturated_every"]] = -1.0
     x0 = 0.5 * syn.emission_profile(V, t=1.0) + 0.1 if c.get("warm_start") else None
     lap = syn.laplacian_coo(V) if c.get("laplacian") else None
+    if lap is not None and c.get("lap_diag_add"):
+        idx, val = lap
+        val = val.copy()
+        val[(idx // np.uint64(V)) == (idx % np.uint64(V))] += np.float32(c["lap_diag_add"])
+        lap = (idx, val)
     return dict(H=H, frames=frames, x0=x0, lap=lap, kw=dict(c["kw"]), no_guess=bool(c.get("no_guess")))
 
 

@@ -40,7 +40,7 @@ def test_config_defaults_are_the_reference_constructor_defaults(sart):
     assert (cfg.ray_density_threshold, cfg.ray_length_threshold, cfg.conv_tolerance) == (1e-6, 1e-6, 1e-5)
     assert (cfg.beta_laplace, cfg.relaxation, cfg.max_iterations) == (1e-2, 1.0, 2000)
     assert (cfg.rank, cfg.nranks, cfg.device, cfg.logarithmic, cfg.semantics) == (0, 1, -1, 0, sart.SEMANTICS_CPU)
-    assert C.sizeof(sart.Config) == 88 and C.sizeof(sart.Stats) == 112
+    assert C.sizeof(sart.Config) == 88 and C.sizeof(sart.Stats) == 160  # sizeof in C (gcc)
 
 
 def test_shard_range_matches_reference_partition(sart, restatement):

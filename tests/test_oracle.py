@@ -118,6 +118,60 @@ def test_generator_scale_and_shard_invariance(restatement):
     np.testing.assert_array_equal(tail, H[48:])
 
 
+def test_line_of_sight_generator(restatement):
+    """The second synthetic kind (SART_SYNTHETIC_LOS): integer arithmetic restated in numpy gives the same bits; rows are
+    rays (a few hundred strong elements in a band) over a weak dense background, with ray lengths of order one."""
+    syn = load_synthetic()
+    P, V, seed = 200, 2500, 42
+    H = restatement.fill_synthetic(P, V, seed, kind=1)
+    nx, nz = syn.voxel_grid_shape(V)
+    M = (1 << 64) - 1
+
+    def splitmix(z):
+        z = (z + 0x9E3779B97F4A7C15) & M
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M
+        return z ^ (z >> 31)
+
+    e = restatement.lib.oracle_los_exponent(V)
+    for i in (0, 1, 57, 199):
+        h = splitmix((seed ^ 0xA5A5A5A55A5A5A5A) ^ ((i * 0xD1342543DE82EF95) & M))
+        h2 = splitmix(h)
+        a = (h & 2047) - 1023
+        b = (1024 - abs(a)) * (1 if (h >> 11) & 1 else -1)
+        c = a * ((h2 & 0xFFFFFF) % nx) + b * (((h2 >> 24) & 0xFFFFFF) % nz)
+        for j in list(range(0, V, 97)) + [V - 1]:
+            d = abs(a * (j // nz) + b * (j % nz) - c)
+            direct = (2048 - d) // 2 if d < 2048 else 0
+            bg = (splitmix((seed + 1) ^ (((i * V + j) * 0xD1342543DE82EF95) & M)) >> 56) | 1
+            assert H[i, j] == np.float32(direct * 1024 + bg) * np.float32(2.0 ** -e)
+    lam = H.sum(axis=1)
+    assert 0.5 < lam.mean() < 1.5 and lam.min() > 1e-3
+    strong = (H > 1024 * 2.0 ** -e).sum(axis=1)
+    assert 20 < np.median(strong) < 0.2 * V  # a band, not the whole row
+    np.testing.assert_array_equal(restatement.fill_synthetic(16, V, seed, row0=100, kind=1), H[100:116])
+
+
+def test_line_of_sight_series_needs_tens_of_iterations(restatement):
+    """What the kind is for (BASELINE configs[3]): on the dense matrix the reference's stopping rule fires after two
+    iterations of a warm-started frame, far from the emission; on this one frames take around ten at 1e-6 and land
+    within a few per cent of it."""
+    syn = load_synthetic()
+    V = 900
+    P = 4 * V
+    H = restatement.fill_synthetic(P, V, 42, kind=1)
+    sums = restatement.ray_sums(H)
+    x, its, errs = None, [], []
+    for k in range(4):
+        truth = syn.emission_profile(V, t=0.002 * k)
+        g = restatement.forward(H, truth)
+        x, st, it = restatement.solve(H, g, x0=x, conv_tolerance=1e-6, beta_laplace=0.0, sums=sums)
+        assert st == 0
+        its.append(it)
+        errs.append(rel_l2(x, truth))
+    assert min(its[1:]) >= 8 and max(errs) < 0.1, (its, errs)
+
+
 def test_laplacian_helper_convention():
     syn = load_synthetic()
     V = 12 * 15

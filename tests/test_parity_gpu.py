@@ -77,6 +77,20 @@ def test_generator_is_bit_identical_to_the_cpu_generator(sart, restatement):
             np.testing.assert_array_equal(eng.download_rows(), ref[off:off + n])
 
 
+def test_line_of_sight_generator_is_bit_identical_to_the_cpu_generator(sart, restatement):
+    P, V = 257, 5000  # 50 x 100 voxel grid; V not a multiple of 32
+    ref = restatement.fill_synthetic(P, V, 42, kind=1)
+    with sart.Engine(P, V, device=0) as eng:
+        eng.fill_synthetic(42, sart.SYNTHETIC_LOS)
+        np.testing.assert_array_equal(eng.download_rows(), ref)
+    off, n = sart.shard_range(P, 3, 2)
+    with sart.Engine(P, V, rank=2, nranks=3, device=0) as eng:
+        eng.fill_synthetic(42, sart.SYNTHETIC_LOS)
+        np.testing.assert_array_equal(eng.download_rows(), ref[off:off + n])
+        with pytest.raises(sart.SartError):
+            eng.fill_synthetic(42, 7)
+
+
 def test_upload_subblocks_roundtrip(sart):
     rng = np.random.default_rng(0)
     P, V = 97, 203
@@ -371,6 +385,65 @@ def test_engine_matches_the_reference_gpu_solver(sart, restatement):
             eng.finalize()
             x = eng.solve(g)[0]
         assert rel_l2(x, x_ref) <= TOL
+
+
+def _rowsum_laplacian(V, add=0.5):
+    idx, val = load_synthetic().laplacian_coo(V)
+    val = val.copy()
+    val[(idx // np.uint64(V)) == (idx % np.uint64(V))] += np.float32(add)
+    return idx, val
+
+
+@BOTH_MODES
+@pytest.mark.parametrize("gpu_sem", [False, True], ids=["cpu-semantics", "gpu-semantics"])
+def test_log_penalty_units_with_nonzero_laplacian_row_sums(gpu_sem, mode, sart, restatement):
+    """The log solver's penalty beta * L * log(x) is not scale-invariant when a Laplacian row does not sum to zero:
+    the CPU solver takes log() of the solution in the caller's units (sartsolver.cpp:292), the GPU solver of the
+    iterate divided by max(g) (sart_kernels.cu:200). A frame 37.5 times brighter than max(g) = 1 tells them apart."""
+    syn = load_synthetic()
+    P, V = 400, 180
+    H = restatement.fill_synthetic(P, V, 31)
+    g = 37.5 * restatement.forward(H, syn.emission_profile(V))
+    lap = _rowsum_laplacian(V)
+    kw = dict(beta_laplace=2e-2, max_iterations=15, fixed_iterations=True, logarithmic=True, relaxation=0.8)
+    x_ref = restatement.solve(H, g, lap=lap, gpu_semantics=gpu_sem, **kw)[0]
+    x_other = restatement.solve(H, g, lap=lap, gpu_semantics=not gpu_sem, **kw)[0]
+    assert rel_l2(x_other, x_ref) > 1e-2  # the two conventions really differ on this input
+    with sart.Engine(P, V, device=0, sweep_mode=mode, semantics=sart.SEMANTICS_GPU if gpu_sem else sart.SEMANTICS_CPU,
+                     **kw) as eng:
+        eng.upload_rows(H)
+        eng.set_laplacian(*lap)
+        eng.finalize()
+        x = eng.solve(g)[0]
+    assert rel_l2(x, x_ref) <= TOL
+
+
+def test_log_solver_matches_the_reference_gpu_solver_on_nonzero_row_sums(sart, restatement):
+    """Pins the GPU-semantics branch of the restatement (and the engine) to the reference's own CUDA log solver where
+    the units of the penalty matter. That solver uses __logf / __powf / __expf (about 1e-6 per step), hence the wider
+    bound; the unit convention is a 1e-2 effect on this input."""
+    import os
+    from oracle.pyoracle import REF_GPU_SO, Reference
+    if not os.path.exists(REF_GPU_SO):
+        pytest.skip("oracle/_ref/libsart_ref_gpu.so not built")
+    syn = load_synthetic()
+    P, V = 2000, 900
+    H = restatement.fill_synthetic(P, V, 78)
+    g = 37.5 * restatement.forward(H, syn.emission_profile(V))
+    lap = _rowsum_laplacian(V)
+    ref = Reference(REF_GPU_SO)
+    x_ref, st_ref, it_ref = ref.solve(H, g, lap=lap, beta_laplace=2e-2, max_iterations=6, conv_tolerance=1e-300,
+                                      logarithmic=True, relaxation=0.8)
+    assert 1 <= it_ref <= 6
+    kw = dict(beta_laplace=2e-2, max_iterations=it_ref, fixed_iterations=True, logarithmic=True, relaxation=0.8)
+    x_res = restatement.solve(H, g, lap=lap, gpu_semantics=True, **kw)[0]
+    assert rel_l2(x_res, x_ref) <= 1e-4
+    with sart.Engine(P, V, device=0, semantics=sart.SEMANTICS_GPU, **kw) as eng:
+        eng.upload_rows(H)
+        eng.set_laplacian(*lap)
+        eng.finalize()
+        x = eng.solve(g)[0]
+    assert rel_l2(x, x_ref) <= 1e-4
 
 
 def test_file_loader_streams_blocks_through_pinned_staging(sart, tmp_path, monkeypatch):
