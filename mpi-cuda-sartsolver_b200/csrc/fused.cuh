@@ -201,9 +201,11 @@ constexpr long long kSpinLimit = 8000000000LL;            // ~4 s at 2 GHz
 constexpr unsigned long long kBarrierPoison = 1ull << 40;  // added to the barrier counter by a CTA that gives up
 
 // true: every CTA arrived; false: this or another CTA timed out (the counter is poisoned so nobody waits again)
-__device__ __forceinline__ bool grid_barrier(unsigned long long* ctr, unsigned long long target, int* s_abort) {
+// (*target: advanced by thread 0 before the call; only thread 0 reads it, behind the first __syncthreads)
+__device__ __forceinline__ bool grid_barrier(unsigned long long* ctr, const unsigned long long* target_ptr, int* s_abort) {
     __syncthreads();
     if (threadIdx.x == 0) {
+        const unsigned long long target = *target_ptr;
         __threadfence();
         atomicAdd(ctr, 1ull);
         const long long t0 = clock64();
@@ -244,6 +246,11 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ int s_abort;
     __shared__ double s_f2, s_f2r[kMaxPeers];
+    // What only the tails between the sweeps need lives in shared memory, not in registers that would stay occupied through
+    // the row loop: the grid-barrier target and the exchange epoch (thread 0 advances them before the barrier that opens a
+    // tail; everybody reads them behind it), and the series block as the launch found it.
+    __shared__ unsigned long long s_bar_target, s_tails, s_epoch0;
+    __shared__ SeriesCtl s_ctl;
 
     double conv_prev = 0.0;
     if constexpr (PERSIST) {
@@ -275,6 +282,17 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
         asm volatile("st.shared.f32 [%0], %1;" ::"r"(cdot_u32 + 4 * i), "f"(0.f) : "memory");
     if (tid == 0) {
         s_abort = 0;
+        s_bar_target = 0;
+        s_tails = 0;
+        if constexpr (PERSIST) {
+            s_epoch0 = sv->epoch0;
+            SeriesCtl c = {};
+            if (sv->series) {  // every CTA reads the block long before CTA 0 rewrites it at the end of the solve
+                c = *sv->series;
+                s_epoch0 = c.epoch;
+            }
+            s_ctl = c;
+        }
         for (uint32_t s = 0; s < S; ++s) {
             mbar_init(full_u32 + 8 * s, 1);
             mbar_init(empty_u32 + 8 * s, NWC);
@@ -292,23 +310,17 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     uint32_t pr_stage = 0, pr_slot = 0, pr_parity = 1;                                    // producer
     uint32_t rd_slot = 0, rd_parity = 0;                                                  // reducer
     uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0, fin_stage = 0, fin_slot = 0, fin_parity = 0;  // consumers
-    unsigned long long bar_target = 0;
 
     int t_spec = -1, pflip = 0, t_first = 0;
     bool repeated = false;
-    unsigned long long tails = 0, epoch0 = 0;
-    SeriesCtl ctl = {};
     if constexpr (PERSIST) {
-        epoch0 = sv->epoch0;
-        if (sv->series) {  // every CTA reads the block long before CTA 0 rewrites it at the end of the solve
-            ctl = *sv->series;
-            epoch0 = ctl.epoch;
-            if (ctl.handed) {
+        if (sv->series) {  // (s_ctl: written before the cluster-wide synchronisation above)
+            if (s_ctl.handed) {
                 t_first = 1;
-                pflip = ctl.pflip;
+                pflip = s_ctl.pflip;
             }
-            const int d = ctl.it_prev - ctl.it_prev2;
-            if (sv->has_next && ctl.it_prev >= 2 && ctl.it_prev2 >= 2 && d >= -2 && d <= 2) t_spec = ctl.it_prev;
+            const int d = s_ctl.it_prev - s_ctl.it_prev2;
+            if (sv->has_next && s_ctl.it_prev >= 2 && s_ctl.it_prev2 >= 2 && d >= -2 && d <= 2) t_spec = s_ctl.it_prev;
         }
     }
     // Rows of the coming sweep whose copies the producer already issued while the previous tail was running: the matrix
@@ -504,8 +516,11 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     tp = now;
                 }
             };
-            bar_target += nblk;
-            bool ok = grid_barrier(sv->gbar, bar_target, &s_abort);
+            if (tid == 0) {
+                s_bar_target += nblk;
+                s_tails += 1;  // one exchange per tail, repeated sweeps included
+            }
+            bool ok = grid_barrier(sv->gbar, &s_bar_target, &s_abort);
             if (timer) sv->tail_ns[2] = global_timer_ns();  // the slowest cluster has finished its rows
             phase_done(0);
             const uint64_t V = sv->V, chunk = (V + nblk - 1) / nblk;
@@ -513,12 +528,13 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             // this rank's partial of voxel j: the clusters' partials in fixed order (reduce_partials_kernel)
             auto local_sum = [&](uint64_t j) {
                 double sj = 0.0;
-                for (uint32_t k0 = 0; k0 < ncl; k0 += 8) {  // eight L2 loads in flight, added in cluster order
-                    float v[8];
+                constexpr uint32_t LB = 8;  // L2 loads in flight, added in cluster order
+                for (uint32_t k0 = 0; k0 < ncl; k0 += LB) {
+                    float v[LB];
 #pragma unroll
-                    for (uint32_t i = 0; i < 8; ++i) v[i] = (k0 + i < ncl) ? __ldcg(a.part + (uint64_t)(k0 + i) * sv->ld + j) : 0.f;
+                    for (uint32_t i = 0; i < LB; ++i) v[i] = (k0 + i < ncl) ? __ldcg(a.part + (uint64_t)(k0 + i) * sv->ld + j) : 0.f;
 #pragma unroll
-                    for (uint32_t i = 0; i < 8; ++i) sj += (double)v[i];
+                    for (uint32_t i = 0; i < LB; ++i) sj += (double)v[i];
                 }
                 return sj;
             };
@@ -529,7 +545,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 if (lane == 0) s_f2 = f;
             }
             const bool multi = sv->nranks > 1;
-            const unsigned long long epoch = epoch0 + (++tails);  // one exchange per tail, repeated sweeps included
+            const unsigned long long tails = s_tails, epoch = s_epoch0 + tails;
             const uint64_t rec = (uint64_t)blk * (chunk + 1);  // this CTA's record in an exchange buffer: [sum(fit^2)][chunk]
             if (ok && multi) {
                 double* mine = reinterpret_cast<double*>(sv->peers[sv->rank] + sv->buf_off[epoch & 1]) + rec;
@@ -599,12 +615,13 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 *sv->st[1] = o;
                 *sv->exchanges = tails;
                 if (sv->series) {
+                    const SeriesCtl ctl = s_ctl;
                     SeriesCtl c = ctl;
                     c.handed = hand_over ? 1 : 0;
                     c.pflip = ((t + 1 + pflip) & 1) ^ 1;  // the next launch's sweep 1 reads what the hand-over writes
                     c.it_prev2 = ctl.it_prev;
                     c.it_prev = t;
-                    c.epoch = epoch0 + tails;
+                    c.epoch = epoch;
                     c.passes = ctl.passes + tails;
                     c.frames_handed = ctl.frames_handed + (hand_over ? 1 : 0);
                     c.sweeps_repeated = ctl.sweeps_repeated + ((int)tails > t - t_first + 1 ? 1 : 0);
@@ -634,11 +651,10 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 break;
             }
             if (!redo) {
-                UpdArgs u = sv->upd;
-                u.xd_cur = sv->xd[(t + pflip) & 1];
-                u.xd_next = sv->xd[(t + 1 + pflip) & 1];
-                u.xf_next = sv->xf[(t + 1 + pflip) & 1];
-                u.out_scale = hand_over ? *sv->out_scale : 1.0;
+                const double* xd_cur = sv->xd[(t + pflip) & 1];
+                double* xd_next = sv->xd[(t + 1 + pflip) & 1];
+                float* xf_next = sv->xf[(t + 1 + pflip) & 1];
+                const double out_scale = hand_over ? *sv->out_scale : 1.0;
                 for (uint64_t j = j0 + tid; j < j1; j += blockDim.x) {
                     double sj;
                     if (multi) {
@@ -658,7 +674,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     } else {
                         sj = local_sum(j);
                     }
-                    apply_update(u, j, sj);
+                    apply_update_at(sv->upd, xd_cur, xd_next, xf_next, out_scale, j, sj);
                 }
             }
             phase_done(multi ? 3 : 1);
@@ -666,8 +682,8 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 drain();
                 break;
             }
-            bar_target += nblk;
-            if (!grid_barrier(sv->gbar, bar_target, &s_abort)) {
+            if (tid == 0) s_bar_target += nblk;
+            if (!grid_barrier(sv->gbar, &s_bar_target, &s_abort)) {
                 drain();
                 if (tid == 0) {
                     IterState o;
@@ -680,7 +696,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                     o.pad = 0;
                     *sv->st[0] = o;
                     *sv->st[1] = o;
-                    *sv->exchanges = tails;
+                    *sv->exchanges = s_tails;
                     if (sv->series) {
                         sv->series->timed_out = 1;
                         if (sv->out_status) *sv->out_status = kStatusExchangeTimeout;

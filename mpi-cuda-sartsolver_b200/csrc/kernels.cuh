@@ -541,34 +541,59 @@ struct UpdArgs {
 
 // x_{t+1,j} from x_t and the reduced back projection s_j of voxel j. x_t is read through L2 (ld.global.cg): in the
 // whole-solve kernel it was written by other SMs earlier in the same launch.
-__device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, double sj) {
+// The iterate's buffers and the output scale are passed apart from the constant fields, so that the whole-solve kernel can
+// hand in its kernel parameter block as it is (no per-sweep copy of the struct in registers).
+__device__ __forceinline__ void apply_update_at(const UpdArgs& a, const double* __restrict__ xd_cur, double* __restrict__ xd_next,
+                                                float* __restrict__ xf_next, double out_scale, uint64_t j, double sj) {
     double pen = 0.0;
     if (a.lap_rowptr) {
-        const int b = a.lap_rowptr[j], e = a.lap_rowptr[j + 1];
+        const int b = __ldg(a.lap_rowptr + j), e = __ldg(a.lap_rowptr + j + 1);
         // The iterate is kept as x / max(g). The linear penalty is scale-covariant; the log solver's is not: the CPU
         // solver takes log() of the solution in the caller's units, so a Laplacian row whose entries do not add up to
         // zero sees the normalisation (beta * log(norm) * rowsum). The GPU solver takes it of the normalised iterate.
         const double unit = (a.log_mode && a.log_caller_units) ? a.fs->norm : 1.0;
-        for (int k = b; k < e; ++k) {
-            const double xv = __ldcg(a.xd_cur + a.lap_col[k]);
-            pen += a.beta * (double)a.lap_val[k] * (a.log_mode ? log(xv * unit) : xv);
+        // Entries of a row in batches: the column indices and values first (read-only for the life of the engine: through
+        // L1, where a CTA of the whole-solve kernel finds its own voxels' rows again every sweep -- the matrix streams
+        // past L1), then the iterate's values (written by other SMs earlier in the launch: through L2), then the sum in
+        // the stored order. Three dependent memory round trips per batch instead of two per entry.
+        constexpr int LAPB = 2;
+        for (int k0 = b; k0 < e; k0 += LAPB) {
+            int col[LAPB];
+            float val[LAPB];
+            double xv[LAPB];
+#pragma unroll
+            for (int i = 0; i < LAPB; ++i)
+                if (k0 + i < e) {
+                    col[i] = __ldg(a.lap_col + k0 + i);
+                    val[i] = __ldg(a.lap_val + k0 + i);
+                }
+#pragma unroll
+            for (int i = 0; i < LAPB; ++i)
+                if (k0 + i < e) xv[i] = __ldcg(xd_cur + col[i]);
+#pragma unroll
+            for (int i = 0; i < LAPB; ++i)
+                if (k0 + i < e) pen += a.beta * (double)val[i] * (a.log_mode ? log(xv[i] * unit) : xv[i]);
         }
     }
-    const double rho = a.ray_density[j];
+    const double rho = __ldg(a.ray_density + j);
     const bool on = rho > a.h_d;
     double xn;
     if (!a.log_mode) {
         const double diff = on ? sj * (a.relax / rho) : 0.0;
-        xn = __ldcg(a.xd_cur + j) + (diff - pen);
+        xn = __ldcg(xd_cur + j) + (diff - pen);
         if (signbit(xn)) xn = 0.0;
     } else {
         const double fitj = on ? sj : 0.0;
         const double eps = a.eps_norm + a.eps_orig / a.fs->norm;
-        xn = __ldcg(a.xd_cur + j) * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
+        xn = __ldcg(xd_cur + j) * pow((a.obs[j] + eps) / (fitj + eps), a.relax) * exp(-pen);
     }
-    xn *= a.out_scale;
-    a.xd_next[j] = xn;
-    a.xf_next[j] = (float)xn;
+    xn *= out_scale;
+    xd_next[j] = xn;
+    xf_next[j] = (float)xn;
+}
+
+__device__ __forceinline__ void apply_update(const UpdArgs& a, uint64_t j, double sj) {
+    apply_update_at(a, a.xd_cur, a.xd_next, a.xf_next, a.out_scale, j, sj);
 }
 
 __global__ void update_kernel(const UpdArgs a) {

@@ -55,67 +55,94 @@ CompositeFrames::CompositeFrames(std::vector<CameraSeries> cams, const std::vect
     if (frame_indices.empty()) throw std::runtime_error("No composite images can be created for given time intervals.");
 }
 
-// source/image.cpp:110-196. Frames of different cameras are combined when they fall on the same point of a time grid of
-// pitch `step` within `threshold`; step 0 = the largest of the cameras' smallest frame spacings; threshold 0 = step.
+// Multi-camera synchronisation (the behaviour of source/image.cpp:110-196, written from its contract, as a gather):
+// a time grid of pitch `step` is laid over the interval, starting one step before the earliest frame of any camera and
+// ending one step after the latest; a composite frame exists at a grid point when EVERY camera has a frame within
+// `threshold` of it. step 0 = the largest of the cameras' smallest frame spacings; threshold 0 = step.
+namespace {
+
+using TimedFrames = std::vector<std::pair<double, size_t>>;  // one camera: (time, frame index), ascending in time
+
+struct TimeGrid {
+    double origin = 0, step = 1, threshold = 1;
+    size_t npoints = 0;
+    double at(size_t k) const { return origin + (double)k * step; }
+    // the grid point a frame belongs to: the nearest one
+    long long home(double t) const { return std::llround((t - origin) / step); }
+};
+
+// The smallest spacing between two consecutive frames of a camera (its whole span when it has a single spacing).
+double finest_spacing(const TimedFrames& frames) {
+    double finest = frames.back().first - frames.front().first;
+    for (size_t i = 1; i < frames.size(); ++i) finest = std::min(finest, frames[i].first - frames[i - 1].first);
+    return finest;
+}
+
+struct NearestFrame {
+    double offset;  // frame time - grid time
+    size_t frame;
+};
+
+// Of the frames whose home is grid point k or one of its two neighbours, the one closest to k. Walking them in time
+// order, a later frame only displaces an earlier one when it is closer by more than kTimeEpsilon (equidistant frames:
+// the earlier one is kept), and nothing further than 1 % beyond the threshold is ever considered.
+NearestFrame nearest_frame(const TimedFrames& frames, const TimeGrid& grid, size_t k) {
+    NearestFrame best{1.01 * grid.threshold, 0};
+    const long long lo = (long long)k - 1, hi = (long long)k + 1;
+    auto it = std::partition_point(frames.begin(), frames.end(), [&](const auto& f) { return grid.home(f.first) < lo; });
+    for (; it != frames.end() && grid.home(it->first) <= hi; ++it) {
+        const double offset = it->first - grid.at(k);
+        if (std::abs(offset) + kTimeEpsilon < std::abs(best.offset)) best = {offset, it->second};
+    }
+    return best;
+}
+
+}  // namespace
+
 void CompositeFrames::add_interval(const std::vector<std::vector<std::pair<double, size_t>>>& timepairs, double step,
                                    double threshold) {
-    for (const auto& tp : timepairs)
-        if (tp.empty()) return;  // a camera without frames in the interval: nothing can be combined
-    double min_time = timepairs.front().front().first, max_time = timepairs.front().back().first;
-    for (const auto& tp : timepairs) {
-        min_time = std::min(tp.front().first, min_time);
-        max_time = std::max(tp.back().first, max_time);
-    }
-    if (step == 0) {
-        if (max_time - min_time < kTimeEpsilon) step = 1.;
-        else
-            for (const auto& tp : timepairs) {
-                double min_diff = tp.back().first - tp.front().first;
-                for (size_t i = 0; i + 1 < tp.size(); ++i) min_diff = std::min(tp[i + 1].first - tp[i].first, min_diff);
-                step = std::max(min_diff, step);
-            }
-    }
-    if (threshold == 0) threshold = step;
-    min_time -= step;  // one spare grid point on either side
-    max_time += step;
-    const size_t nslots = (size_t)std::llround((max_time - min_time) / step) + 1;
     const size_t ncam = timepairs.size();
+    if (ncam == 0) return;
+    double earliest = 0, latest = 0;
+    for (size_t cam = 0; cam < ncam; ++cam) {
+        if (timepairs[cam].empty()) return;  // a camera without frames in the interval: nothing can be combined
+        const double first = timepairs[cam].front().first, last = timepairs[cam].back().first;
+        earliest = cam ? std::min(earliest, first) : first;
+        latest = cam ? std::max(latest, last) : last;
+    }
+    TimeGrid grid;
+    if (step != 0) grid.step = step;
+    else if (latest - earliest < kTimeEpsilon) grid.step = 1.;  // every frame at the same instant
+    else {
+        grid.step = 0;
+        for (const auto& frames : timepairs) grid.step = std::max(grid.step, finest_spacing(frames));
+    }
+    grid.threshold = threshold != 0 ? threshold : grid.step;
+    grid.origin = earliest - grid.step;
+    grid.npoints = (size_t)std::llround((latest + grid.step - grid.origin) / grid.step) + 1;
 
-    // per (grid point, camera): signed distance of the closest frame and its index
-    std::vector<std::pair<double, size_t>> grid(nslots * ncam, std::make_pair(1.01 * threshold, (size_t)0));
-    for (size_t cam = 0; cam < ncam; ++cam)
-        for (const auto& tp : timepairs[cam]) {
-            const long long slot = std::llround((tp.first - min_time) / step);
-            for (int d = -1; d <= 1; ++d) {
-                const size_t idx = ncam * (size_t)(slot + d) + cam;
-                const double delta = tp.first - min_time - (double)(slot + d) * step;
-                // "+ epsilon": of two equally distant frames the earlier one wins
-                if (std::abs(delta) + kTimeEpsilon < std::abs(grid[idx].first)) grid[idx] = {delta, tp.second};
-            }
+    std::vector<size_t> chosen(ncam);
+    std::vector<double> chosen_time(ncam);
+    double previous_misfit = 0;  // summed |offset| of the last grid point that had a frame of every camera
+    for (size_t k = 1; k + 1 < grid.npoints; ++k) {  // the first and the last point are the spare ones
+        double misfit = 0;
+        size_t cam = 0;
+        for (; cam < ncam; ++cam) {
+            const NearestFrame pick = nearest_frame(timepairs[cam], grid, k);
+            if (std::abs(pick.offset) > grid.threshold + kTimeEpsilon) break;
+            chosen[cam] = pick.frame;
+            chosen_time[cam] = grid.at(k) + pick.offset;
+            misfit += std::abs(pick.offset);
         }
-
-    double last_delta = 0;
-    for (size_t slot = 1; slot + 1 < nslots; ++slot) {
-        std::vector<size_t> idx;
-        std::vector<double> cam_time;
-        const double ftime = min_time + (double)slot * step;
-        double total_delta = 0;
-        for (size_t cam = 0; cam < ncam; ++cam) {
-            const auto& cell = grid[ncam * slot + cam];
-            if (std::abs(cell.first) > threshold + kTimeEpsilon) break;
-            idx.push_back(cell.second);
-            cam_time.push_back(ftime + cell.first);
-            total_delta += std::abs(cell.first);
+        if (cam < ncam) continue;  // some camera has nothing close enough
+        if (frame_indices.empty() || chosen != frame_indices.back()) {
+            frame_indices.push_back(chosen);
+            camera_time.push_back(chosen_time);
+            time.push_back(grid.at(k));
+        } else if (misfit + kTimeEpsilon < previous_misfit) {
+            time.back() = grid.at(k);  // the same frames again, and this grid point fits them better than the one before
         }
-        if (idx.size() != ncam) continue;
-        if (frame_indices.empty() || idx != frame_indices.back()) {
-            frame_indices.push_back(idx);
-            camera_time.push_back(cam_time);
-            time.push_back(ftime);
-        } else if (total_delta + kTimeEpsilon < last_delta) {
-            time.back() = ftime;  // the same frames sit closer to this grid point than to the previous one
-        }
-        last_delta = total_delta;
+        previous_misfit = misfit;
     }
 }
 

@@ -66,3 +66,41 @@ def test_slower_camera_sets_the_step(tmp_path):
 def test_unsorted_timeline_is_rejected(tmp_path):
     rc, err = timesync(tmp_path, "", [0.0, 2.0, 1.0])
     assert rc == 1 and "not sorted by time" in err
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_timelines_select_what_the_reference_selects(tmp_path, seed):
+    """The driver's synchronisation (a search per grid point) against the restatement of the reference's own routine
+    (oracle/timesync_oracle.py, source/image.cpp:83-196: it scatters every frame onto its grid point and the two
+    neighbours): same composite frames, same camera frames in each, same time stamps -- jittered cameras of different
+    rates, dropped frames, explicit and default step / threshold, several intervals."""
+    from oracle.timesync_oracle import composite_frames
+    rng = np.random.default_rng(100 + seed)
+    ncam = int(rng.integers(1, 4))
+    timelines = []
+    for _ in range(ncam):
+        period = float(rng.choice([0.5, 1.0, 1.0, 2.0]))
+        n = int(rng.integers(3, 30))
+        t = 0.25 * rng.random() + period * np.arange(n) + rng.normal(0, 0.08 * period, n) * (rng.random() < 0.7)
+        t = np.sort(np.round(np.abs(t), 6))
+        t = t[rng.random(len(t)) > 0.15] if len(t) > 4 else t  # dropped frames
+        t = np.unique(t)
+        timelines.append([float(v) for v in t])
+    choice = seed % 4
+    if choice == 0:
+        spec, intervals = "", [(0.0, float("inf"), 0.0, 0.0)]
+    elif choice == 1:
+        spec, intervals = "0:100:1:0.3", [(0.0, 100.0, 1.0, 0.3)]
+    elif choice == 2:
+        spec, intervals = "1:6,7.5:40:0.5", [(1.0, 6.0, 0.0, 0.0), (7.5, 40.0, 0.5, 0.0)]
+    else:
+        spec, intervals = "0:50:2:2.5", [(0.0, 50.0, 2.0, 2.5)]
+    want_idx, want_cam_t, want_t = composite_frames(timelines, intervals)
+    rc, got = timesync(tmp_path, spec, *timelines)
+    if not want_idx:
+        assert rc == 1 and "No composite images can be created" in got
+        return
+    assert rc == 0, got
+    assert [f["indices"] for f in got] == want_idx
+    assert np.allclose([f["time"] for f in got], want_t, rtol=0, atol=1e-9)
+    assert np.allclose([f["camera_time"] for f in got], want_cam_t, rtol=0, atol=1e-9)
