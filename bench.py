@@ -687,14 +687,14 @@ def run_series_arm(args, cp):
         cb.pop("sample_seconds", None)
         cb.pop("sample_iterations", None)
     ok = len(set(hashes)) == 1 and all(v == 0 for v in sts)
+    h2d_all, d2h_all = int(cp.sum(h2d)), int(cp.sum(d2h))  # (collectives: every rank)
     if cp.rank == 0:
         line = {
             "metric": METRIC, "value": total_it / (total_ms / 1e3), "unit": UNIT, "n_gpus": cp.world, "steps": 1,
             "warmup": 1, "ms_per_step": total_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": dict(workload_config(args, cp.world), sweep="fused", exchange=exchange_mode, chunk=chunk),
-            "e2e": {"value": total_it / wall_s, "unit": UNIT, "h2d_bytes_per_step": int(cp.sum(h2d) if cp.world > 1 else h2d),
-                    "d2h_bytes_per_step": int(cp.sum(d2h) if cp.world > 1 else d2h),
+            "e2e": {"value": total_it / wall_s, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
                     "timing": "host wall clock around the sart_solve_series calls (pinned host frames in, solutions out), max over ranks"},
             "series": {"frames": F, "frames_per_s": F / (total_ms / 1e3), "frames_per_s_e2e": F / wall_s,
                        "iterations_total": total_it, "iterations_median": float(np.median(its)),

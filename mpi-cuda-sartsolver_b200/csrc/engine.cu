@@ -144,7 +144,6 @@ struct sart_engine {
     int last_prologue_sweeps = 0;               // matrix passes of the last frame's set-up (initial guess, log "obs")
     // warm-started series (sart_solve_series): look-ahead buffers for the next frame, allocated on first use
     double* d_series_in = nullptr;    // [capacity][P] the chunk's measurements, uploaded once
-    FrameScalars* d_fs_next = nullptr;
     float* d_gspec = nullptr;
     double* d_spec_scale = nullptr;
     SeriesCtl* d_series_ctl = nullptr;
@@ -152,6 +151,13 @@ struct sart_engine {
     int* d_series_res = nullptr;      // [2][capacity] status, iterations
     int32_t series_capacity = 0;
     uint64_t xchg_cta_flag_off = 0;             // per-CTA flags of the in-kernel exchange inside a region
+    // frame statistics (max g, sum g^2) of up to stat_capacity frames: per-CTA partials, reduced values, exchange over peers
+    StatPair* d_stat_part = nullptr;
+    double *d_stat_max = nullptr, *d_stat_sum = nullptr;
+    int32_t stat_capacity = 0;
+    uint32_t stat_blocks = 1;
+    uint64_t xchg_stat_flag_off = 0, xchg_stat_slot_off[2] = {0, 0};
+    unsigned long long stat_epoch = 0;
 
     cudaEvent_t ev_solve0 = nullptr, ev_solve1 = nullptr, ev_it0 = nullptr;
     cudaEvent_t ev_batch[2] = {nullptr, nullptr};
@@ -775,9 +781,59 @@ int backproject_weights(sart_engine* e) {
     return SART_OK;
 }
 
-int launch_prepare(sart_engine* e, int weights_mode, const double* gd) {
+// Statistics of nframes frames (gd: [nframes][frame_stride] raw measurements on the device) into d_stat_max / d_stat_sum
+// [first .. first + nframes): max g and sum over g > 0 of g^2 over ALL ranks. Two kernels for all the frames together; with
+// the peers mapped the second one also does the exchange, otherwise the two arrays are all-reduced.
+int compute_frame_stats(sart_engine* e, const double* gd, uint64_t frame_stride, int32_t nframes, int32_t first = 0) {
+    if (first + nframes > e->stat_capacity) {
+        if (first != 0) return fail(SART_ERR_STATE, "statistics buffer too small (internal error)");
+        for (void* p : {(void*)e->d_stat_part, (void*)e->d_stat_max, (void*)e->d_stat_sum})
+            if (p) CUDA_TRY(cudaFree(p));
+        e->d_stat_part = nullptr;
+        e->d_stat_max = e->d_stat_sum = nullptr;
+        e->stat_capacity = 0;
+        // enough CTAs to stream a frame at memory speed, few enough that the second stage stays trivial
+        e->stat_blocks = (uint32_t)std::min<uint64_t>(64, std::max<uint64_t>(1, ceil_div(e->P, 8192)));
+        const int32_t cap = std::max<int32_t>(nframes, 4);
+        SART_TRY(dev_alloc(&e->d_stat_part, (uint64_t)cap * e->stat_blocks, false));
+        SART_TRY(dev_alloc(&e->d_stat_max, (uint64_t)cap));
+        SART_TRY(dev_alloc(&e->d_stat_sum, (uint64_t)cap));
+        e->stat_capacity = cap;
+    }
+    const bool multi = e->cfg.nranks > 1;
+    for (int32_t f0 = 0; f0 < nframes; f0 += kStatSlots) {
+        const int32_t n = std::min<int32_t>(kStatSlots, nframes - f0);
+        StatPair* part = e->d_stat_part + (uint64_t)(first + f0) * e->stat_blocks;
+        frame_stats_partial_kernel<<<dim3(e->stat_blocks, (uint32_t)n), 1024, 0, e->stream>>>(gd + (uint64_t)f0 * frame_stride, e->P,
+                                                                                              frame_stride, part);
+        CUDA_TRY(cudaGetLastError());
+        StatXchg x = {};
+        if (multi && e->peer_exchange) {
+            x.peers = e->d_peers;
+            x.nranks = (uint32_t)e->cfg.nranks;
+            x.rank = (uint32_t)e->cfg.rank;
+            x.epoch = ++e->stat_epoch;  // every rank makes the same calls in the same order
+            x.flag_off = e->xchg_stat_flag_off;
+            x.slot_off[0] = e->xchg_stat_slot_off[0];
+            x.slot_off[1] = e->xchg_stat_slot_off[1];
+        }
+        frame_stats_final_kernel<<<1, 1024, 0, e->stream>>>(part, e->stat_blocks, (uint32_t)n, e->d_stat_max + first + f0,
+                                                            e->d_stat_sum + first + f0, x);
+        CUDA_TRY(cudaGetLastError());
+        e->launches += 2;
+        if (multi && !e->peer_exchange) {
+            SART_TRY(allreduce_f64(e, e->d_stat_max + first + f0, (uint64_t)n, ncclMax));
+            SART_TRY(allreduce_f64(e, e->d_stat_sum + first + f0, (uint64_t)n, ncclSum));
+        }
+    }
+    return SART_OK;
+}
+
+// stat: index of the frame's statistics in d_stat_max / d_stat_sum
+int launch_prepare(sart_engine* e, int weights_mode, const double* gd, int32_t stat = 0) {
     frame_prepare_kernel<<<(uint32_t)ceil_div(e->P, 256), 256, 0, e->stream>>>(
-        gd, e->P, e->d_fs, e->d_lambda, e->cfg.ray_length_threshold, e->d_g, e->d_rinv, e->d_w, weights_mode);
+        gd, e->P, e->d_fs, e->d_stat_max + stat, e->d_stat_sum + stat, e->d_lambda, e->cfg.ray_length_threshold, e->d_g, e->d_rinv,
+        e->d_w, weights_mode);
     CUDA_TRY(cudaGetLastError());
     ++e->launches;
     return SART_OK;
@@ -816,6 +872,10 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
     e->stats.solve_launches = 1;
     e->stats.tail_ms_avg = tail[1] ? 1e-6 * (double)tail[0] / (double)tail[1] : 0;
     for (int k = 0; k < kTailPhases; ++k) e->stats.tail_phase_us[k] = tail[1] ? 1e-3 * (double)phase[k] / (double)tail[1] : 0;
+    if (env_int("SART_TAIL_DEBUG", 0) && tail[1])
+        std::fprintf(stderr, "sart tail debug (us per sweep, thread 0 of CTA 0): own cluster sum %.2f, own update %.2f, before them %.2f\n",
+                     1e-3 * (double)phase[5] / (double)tail[1], 1e-3 * (double)phase[6] / (double)tail[1],
+                     1e-3 * (double)phase[7] / (double)tail[1]);
     e->stats.sweep_mode = SART_SWEEP_FUSED;
     e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE : SART_EXCHANGE_PEER;
     if (e->profiling) {
@@ -829,28 +889,29 @@ int finish_persistent_solve(sart_engine* e, int sweeps_before, uint32_t vblocks)
 // Per-frame set-up from the staged measurement d_gd (and d_xio when has_guess): statistics, normalisation, starting
 // solution into buffer 0, fresh control blocks. *sweeps counts the matrix passes it took (initial guess, log "obs").
 // gd: the frame's raw measurement on the device (default: the staging buffer d_gd).
-int frame_prologue(sart_engine* e, int has_guess, int* sweeps, const SeriesCtl* series = nullptr, const double* gd = nullptr) {
+// stat >= 0: the frame's statistics are already in d_stat_max / d_stat_sum [stat] (a series computes them for the whole chunk).
+int frame_prologue(sart_engine* e, int has_guess, int* sweeps, const SeriesCtl* series = nullptr, const double* gd = nullptr,
+                   int32_t stat = -1) {
     if (!gd) gd = e->d_gd;
     const uint32_t vblocks = (uint32_t)ceil_div(e->V, 256);
     const bool gpu_sem = e->cfg.semantics == SART_SEMANTICS_GPU;
     const bool log_mode = e->cfg.logarithmic != 0;
 
-    frame_stats_kernel<<<1, 1024, 0, e->stream>>>(gd, e->P, e->d_fs);
-    CUDA_TRY(cudaGetLastError());
-    ++e->launches;
-    SART_TRY(allreduce_f64(e, &e->d_fs->gmax, 1, ncclMax));
-    SART_TRY(allreduce_f64(e, &e->d_fs->gsq, 1, ncclSum));
+    if (stat < 0) {
+        SART_TRY(compute_frame_stats(e, gd, e->P, 1));
+        stat = 0;
+    }
 
     *sweeps = 0;
     if (log_mode) {
-        SART_TRY(launch_prepare(e, 3, gd));
+        SART_TRY(launch_prepare(e, 3, gd, stat));
         SART_TRY(backproject_weights(e));
         mask_obs_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_sred, e->d_rho, e->cfg.ray_density_threshold, e->d_obs, e->V);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
         ++*sweeps;
     }
-    SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1), gd));
+    SART_TRY(launch_prepare(e, has_guess ? 0 : (gpu_sem ? 2 : 1), gd, stat));
     if (!has_guess) {
         SART_TRY(backproject_weights(e));
         ++*sweeps;
@@ -1055,15 +1116,13 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
     };
 
     // per frame: statistics, normalisation, weights of the default initial guess; one pass back-projects all of them
+    SART_TRY(compute_frame_stats(e, e->d_pgd, P, nf));  // all frames of the group together
     for (int f = 0; f < nf; ++f) {
-        frame_stats_kernel<<<1, 1024, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f);
-        SART_TRY(allreduce_f64(e, &e->d_pfs[f].gmax, 1, ncclMax));
-        SART_TRY(allreduce_f64(e, &e->d_pfs[f].gsq, 1, ncclSum));
-        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_lambda,
-                                                             e->cfg.ray_length_threshold, e->d_pg + f * P, e->d_rinv,
+        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_stat_max + f, e->d_stat_sum + f,
+                                                             e->d_lambda, e->cfg.ray_length_threshold, e->d_pg + f * P, e->d_rinv,
                                                              e->d_pw + f * P, gpu_sem ? 2 : 1);
         CUDA_TRY(cudaGetLastError());
-        e->launches += 2;
+        ++e->launches;
     }
     SART_TRY(back_project(nullptr));
     for (int f = 0; f < nf; ++f) {
@@ -1278,13 +1337,19 @@ int setup_peer_exchange(sart_engine* e) {
     NcclApi* api = nccl_api();
     const char* mode = std::getenv("SART_EXCHANGE");
     int ok = !(mode && std::string(mode) == "nccl") && e->cfg.nranks <= kMaxPeers;
-    // [one flag per rank, 128 B apart][one flag per rank and CTA of the whole-solve kernel][buffer 0][buffer 1]
+    // [one flag per rank, 128 B apart][one flag per rank and CTA of the whole-solve kernel][statistics: one flag per rank,
+    // two slot arrays][buffer 0][buffer 1]
     // a buffer holds V + 1 doubles (per-sweep kernels) or one record [sum(fit^2)][chunk] per CTA (whole-solve kernel)
     const uint64_t nblk = std::max<uint64_t>((uint64_t)e->fu_cluster * (e->persistent ? e->fs_nclusters : e->fu_nclusters), 1);
     const uint64_t rank_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
-    const uint64_t flags_bytes = rank_flags_bytes + ceil_div((uint64_t)e->cfg.nranks * nblk * 8, 256) * 256;
+    const uint64_t cta_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * nblk * 8, 256) * 256;
+    const uint64_t stat_slots_bytes = ceil_div((uint64_t)kStatSlots * sizeof(StatPair), 256) * 256;
+    const uint64_t flags_bytes = rank_flags_bytes + cta_flags_bytes + rank_flags_bytes + 2 * stat_slots_bytes;
     const uint64_t buf_bytes = ceil_div((e->V + 2 * nblk + 2) * sizeof(double), 256) * 256;
     e->xchg_cta_flag_off = rank_flags_bytes;
+    e->xchg_stat_flag_off = rank_flags_bytes + cta_flags_bytes;
+    e->xchg_stat_slot_off[0] = e->xchg_stat_flag_off + rank_flags_bytes;
+    e->xchg_stat_slot_off[1] = e->xchg_stat_slot_off[0] + stat_slots_bytes;
     e->xchg_buf_off[0] = flags_bytes;
     e->xchg_buf_off[1] = flags_bytes + buf_bytes;
 
@@ -1347,6 +1412,7 @@ int setup_peer_exchange(sart_engine* e) {
     SART_TRY(dev_alloc(&e->d_peers, (uint64_t)n, false));
     CUDA_TRY(cudaMemcpy(e->d_peers, peers.data(), sizeof(char*) * n, cudaMemcpyHostToDevice));
     e->xchg_epoch = 0;
+    e->stat_epoch = 0;
     e->peer_exchange = true;
     return SART_OK;
 }
@@ -1365,7 +1431,8 @@ void free_engine(sart_engine* e) {
     if (e->d_peers) cudaFree(e->d_peers);
     if (e->d_solve_ctl) cudaFree(e->d_solve_ctl);
     if (e->h_solve_ctl) cudaFreeHost(e->h_solve_ctl);
-    void* series_ptrs[] = {e->d_series_in, e->d_fs_next, e->d_gspec, e->d_spec_scale, e->d_series_ctl, e->d_series_out, e->d_series_res};
+    void* series_ptrs[] = {e->d_series_in, e->d_gspec, e->d_spec_scale, e->d_series_ctl, e->d_series_out, e->d_series_res,
+                           e->d_stat_part, e->d_stat_max, e->d_stat_sum};
     for (void* p : series_ptrs)
         if (p) cudaFree(p);
     void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
@@ -1878,8 +1945,7 @@ static int solve_series_impl(sart_engine* e, int32_t nframes, const double* meas
         e->stats.fused_launches = total_fused;
         e->stats.fp_launches = e->stats.bp_launches = 0;
     } else {
-        if (!e->d_fs_next) {
-            SART_TRY(dev_alloc(&e->d_fs_next, 1));
+        if (!e->d_gspec) {
             SART_TRY(dev_alloc(&e->d_gspec, e->P));
             SART_TRY(dev_alloc(&e->d_spec_scale, 1));
             SART_TRY(dev_alloc(&e->d_series_ctl, 1));
@@ -1903,23 +1969,22 @@ static int solve_series_impl(sart_engine* e, int32_t nframes, const double* meas
         // the whole chunk of measurements in one copy: nothing the host does per frame waits for the device afterwards
         CUDA_TRY(cudaMemcpyAsync(e->d_series_in, measurements, (uint64_t)nframes * e->P * sizeof(double), cudaMemcpyHostToDevice, e->stream));
         h2d += (uint64_t)nframes * e->P * sizeof(double);
+        // statistics of every frame of the chunk in one go: no collective is left inside the frame loop
+        SART_TRY(compute_frame_stats(e, e->d_series_in, e->P, nframes));
         int setup_sweeps = 0;
         for (int32_t f = 0; f < nframes; ++f) {
             const bool more = f + 1 < nframes;
             int sweeps = 0;
             // set-up of frame f; its starting solution is left alone on the device when frame f - 1 handed x_1 over
             const double* gd = e->d_series_in + (uint64_t)f * e->P;
-            SART_TRY(frame_prologue(e, (f > 0 || guess) ? 1 : 0, &sweeps, e->d_series_ctl, gd));
+            SART_TRY(frame_prologue(e, (f > 0 || guess) ? 1 : 0, &sweeps, e->d_series_ctl, gd, f));
             setup_sweeps += sweeps;
             if (more) {  // look-ahead: the next frame's measurement in this frame's normalisation
                 const double* gd_next = gd + e->P;
-                frame_stats_kernel<<<1, 1024, 0, e->stream>>>(gd_next, e->P, e->d_fs_next);
-                CUDA_TRY(cudaGetLastError());
-                SART_TRY(allreduce_f64(e, &e->d_fs_next->gmax, 1, ncclMax));
-                series_lookahead_kernel<<<pblocks, 256, 0, e->stream>>>(gd_next, e->P, e->d_fs, e->d_fs_next, e->d_gspec,
+                series_lookahead_kernel<<<pblocks, 256, 0, e->stream>>>(gd_next, e->P, e->d_fs, e->d_stat_max + f + 1, e->d_gspec,
                                                                         e->d_spec_scale);
                 CUDA_TRY(cudaGetLastError());
-                e->launches += 2;
+                ++e->launches;
             }
             SeriesLaunch sl;
             sl.ctl = e->d_series_ctl;

@@ -527,15 +527,20 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             const uint64_t j0 = min(V, (uint64_t)blk * chunk), j1 = min(V, j0 + chunk);
             // this rank's partial of voxel j: the clusters' partials in fixed order (reduce_partials_kernel)
             auto local_sum = [&](uint64_t j) {
+                // whole batches of LB unconditional L2 loads in flight, then the rest one by one; added in cluster order
                 double sj = 0.0;
-                constexpr uint32_t LB = 8;  // L2 loads in flight, added in cluster order
-                for (uint32_t k0 = 0; k0 < ncl; k0 += LB) {
+                constexpr uint32_t LB = 8;
+                const uint64_t stride = sv->ld;
+                const float* p = a.part + j;
+                uint32_t k = 0;
+                for (; k + LB <= ncl; k += LB, p += LB * stride) {
                     float v[LB];
 #pragma unroll
-                    for (uint32_t i = 0; i < LB; ++i) v[i] = (k0 + i < ncl) ? __ldcg(a.part + (uint64_t)(k0 + i) * sv->ld + j) : 0.f;
+                    for (uint32_t i = 0; i < LB; ++i) v[i] = __ldcg(p + i * stride);
 #pragma unroll
                     for (uint32_t i = 0; i < LB; ++i) sj += (double)v[i];
                 }
+                for (; k < ncl; ++k, p += stride) sj += (double)__ldcg(p);
                 return sj;
             };
             if (ok && warp == 0) {
@@ -672,9 +677,16 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                                 if (r0 + r < (int)sv->nranks) sj += pr[r];
                         }
                     } else {
+                        const unsigned long long d0 = (timer && j == j0) ? global_timer_ns() : 0ull;
                         sj = local_sum(j);
+                        if (timer && j == j0) {  // diagnostics (SART_TAIL_DEBUG): thread 0's own sum over the clusters
+                            sv->phase_ns[5] += global_timer_ns() - d0;
+                            sv->phase_ns[7] += d0 - tp;  // what came before it in this phase (sum(fit^2), decision)
+                        }
                     }
+                    const unsigned long long d1 = (timer && j == j0) ? global_timer_ns() : 0ull;
                     apply_update_at(sv->upd, xd_cur, xd_next, xf_next, out_scale, j, sj);
+                    if (timer && j == j0) sv->phase_ns[6] += global_timer_ns() - d1;  // ... and its own update
                 }
             }
             phase_done(multi ? 3 : 1);

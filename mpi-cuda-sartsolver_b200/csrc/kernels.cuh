@@ -72,6 +72,21 @@ __device__ __forceinline__ double warp_max(double v) {
     return v;
 }
 
+// Exchange regions mapped between the ranks of one box (CUDA IPC): flags are kFlagStride bytes apart, written with
+// system-scope release stores into every peer's region and polled with acquire loads in one's own.
+constexpr int kMaxPeers = 16;
+constexpr int kFlagStride = 128;
+constexpr int kStatSlots = 1024;  // frames per statistics exchange (a longer chunk goes in several rounds)
+
+__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // Forward projection: fit_i = sum_j H_ij x_j over the local rows  (replaces cublasSgemv, sartsolver_cuda.cpp:188-189,
 // 248-249; CPU twin sartsolver.cpp:166-173, 213-220), with in its epilogue
@@ -621,8 +636,6 @@ __global__ void update_kernel(const UpdArgs a) {
 // the sweep in between, which every peer only signals once it has finished reading buffer b.
 // A peer that never arrives (crashed rank) ends the wait after ~4 s with status SART_STATUS_EXCHANGE_TIMEOUT.
 // ---------------------------------------------------------------------------------------------------------------------
-constexpr int kMaxPeers = 16;
-constexpr int kFlagStride = 128;
 constexpr int kStatusExchangeTimeout = -3;
 
 struct XchgArgs {
@@ -635,15 +648,6 @@ struct XchgArgs {
     double tol;
     int max_iter, fixed, t;
 };
-
-__device__ __forceinline__ void st_release_sys_u64(unsigned long long* p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
 
 __global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs x, const UpdArgs u) {
     const IterState s = *x.st_in;
@@ -720,24 +724,40 @@ __global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs 
 // ---------------------------------------------------------------------------------------------------------------------
 // Per-frame prologue / epilogue (replaces pre_iteration_setup, sartsolver_cuda.cpp:138-194, and :264-265).
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void frame_stats_kernel(const double* __restrict__ g, uint64_t P, FrameScalars* fs) {
+// Frame statistics (max g and sum over g > 0 of g^2: sartsolver_cuda.cpp:147-157, sartsolver.cpp:161-164) in two stages
+// and for any number of frames at once -- a whole chunk of a series, the frames of a batch, or one frame:
+//   frame_stats_partial_kernel  grid (nb, nframes): CTA (b, f) reduces slice b of frame f (four accumulators per thread,
+//                               warp tree, warps in order: a fixed summation order);
+//   frame_stats_final_kernel    one CTA: per frame the nb partials in order, then -- with several ranks -- the ranks' values
+//                               in rank order straight out of each other's exchange regions (one flag round trip for all
+//                               the frames together, like xchg_decide_update_kernel below), so that a frame costs no
+//                               ncclAllReduce at all. Without mapped peers the caller all-reduces the two arrays instead.
+// They replace one single-CTA pass per frame plus two (series: three) scalar all-reduces per frame.
+struct StatPair {
+    double gmax, gsq;
+};
+
+__global__ void __launch_bounds__(1024) frame_stats_partial_kernel(const double* __restrict__ g, uint64_t P, uint64_t frame_stride,
+                                                                    StatPair* __restrict__ part) {
     __shared__ double smax[32], ssum[32];
-    // four independent accumulators per thread: the loop is latency-bound (one CTA, fixed summation order)
+    const uint32_t nb = gridDim.x, b = blockIdx.x, f = blockIdx.y;
+    const uint64_t span = (P + nb - 1) / nb, i0 = min(P, (uint64_t)b * span), i1 = min(P, i0 + span);
+    const double* __restrict__ gf = g + (uint64_t)f * frame_stride;
     double mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, sm[4] = {0.0, 0.0, 0.0, 0.0};
     const uint64_t stride = blockDim.x;
-    uint64_t i = threadIdx.x;
-    for (; i + 3 * stride < P; i += 4 * stride) {
+    uint64_t i = i0 + threadIdx.x;
+    for (; i + 3 * stride < i1; i += 4 * stride) {
         double v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = g[i + u * stride];
+        for (int u = 0; u < 4; ++u) v[u] = gf[i + u * stride];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             mx[u] = fmax(mx[u], v[u]);
             sm[u] += (v[u] > 0) ? v[u] * v[u] : 0.0;
         }
     }
-    for (; i < P; i += stride) {
-        const double v = g[i];
+    for (; i < i1; i += stride) {
+        const double v = gf[i];
         mx[0] = fmax(mx[0], v);
         sm[0] += (v > 0) ? v * v : 0.0;
     }
@@ -756,22 +776,76 @@ __global__ void frame_stats_kernel(const double* __restrict__ g, uint64_t P, Fra
             m = fmax(m, smax[k]);
             s += ssum[k];
         }
-        fs->gmax = m;
-        fs->gsq = s;
+        part[(uint64_t)f * nb + b] = {m, s};
+    }
+}
+
+struct StatXchg {
+    char* const* peers;  // [nranks] exchange regions as mapped here; null: this rank's values only
+    uint32_t nranks, rank;
+    unsigned long long epoch;  // of this exchange; slots alternate with its parity
+    uint64_t flag_off;         // byte offset of the statistics flags [nranks] (kFlagStride apart) inside a region
+    uint64_t slot_off[2];      // byte offsets of the two slot arrays [kStatSlots] StatPair
+};
+
+__global__ void __launch_bounds__(1024) frame_stats_final_kernel(const StatPair* __restrict__ part, uint32_t nb, uint32_t nframes,
+                                                                  double* __restrict__ gmax, double* __restrict__ gsq, const StatXchg x) {
+    // this rank's value of frame f = threadIdx.x (nframes <= kStatSlots <= blockDim.x)
+    const uint32_t f = threadIdx.x;
+    double m = -INFINITY, s = 0.0;
+    if (f < nframes) {
+        const StatPair* p = part + (uint64_t)f * nb;
+        for (uint32_t b = 0; b < nb; ++b) {
+            m = fmax(m, p[b].gmax);
+            s += p[b].gsq;
+        }
+    }
+    if (x.peers) {
+        StatPair* mine = reinterpret_cast<StatPair*>(x.peers[x.rank] + x.slot_off[x.epoch & 1]);
+        if (f < nframes) mine[f] = {m, s};
+        __threadfence_system();
+        __syncthreads();
+        if (f < x.nranks) {
+            st_release_sys_u64(reinterpret_cast<unsigned long long*>(x.peers[f] + x.flag_off + (uint64_t)x.rank * kFlagStride), x.epoch);
+            const unsigned long long* flag =
+                reinterpret_cast<const unsigned long long*>(x.peers[x.rank] + x.flag_off + (uint64_t)f * kFlagStride);
+            const long long t0 = clock64();
+            while (ld_acquire_sys_u64(flag) < x.epoch)
+                if (clock64() - t0 > 8000000000LL) break;  // a dead peer: the solve's own exchange reports it
+        }
+        __syncthreads();
+        if (f < nframes) {
+            m = -INFINITY;
+            s = 0.0;
+            for (uint32_t r = 0; r < x.nranks; ++r) {  // rank order: every rank gets the same bits
+                const StatPair* theirs = reinterpret_cast<const StatPair*>(x.peers[r] + x.slot_off[x.epoch & 1]);
+                const double pm = __ldcv(&theirs[f].gmax), ps = __ldcv(&theirs[f].gsq);
+                m = fmax(m, pm);
+                s += ps;
+            }
+        }
+    }
+    if (f < nframes) {
+        gmax[f] = m;
+        gsq[f] = s;
     }
 }
 
 // weights_mode: 0 none, 1 initial guess CPU semantics (w = g), 2 initial guess GPU semantics (w = max(g, 0)),
 //               3 log solver's back-projected measurement (w = [g >= 0] g / lambda)
+// stat_max / stat_sum: this frame's max g and sum over g > 0 of g^2 over all ranks (frame_stats_final_kernel)
 __global__ void frame_prepare_kernel(const double* __restrict__ gd, uint64_t P, FrameScalars* fs,
+                                     const double* __restrict__ stat_max, const double* __restrict__ stat_sum,
                                      const double* __restrict__ ray_length, double h_l, float* __restrict__ g,
                                      float* __restrict__ rinv, float* __restrict__ w, int weights_mode) {
-    const double gmax = fs->gmax;
+    const double gmax = *stat_max;
     const double norm = (gmax > 0) ? gmax : 1.0;
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i == 0) {
+        fs->gmax = gmax;
+        fs->gsq = *stat_sum;
         fs->norm = norm;
-        fs->m2 = fs->gsq / (norm * norm);
+        fs->m2 = *stat_sum / (norm * norm);
     }
     if (i >= P) return;
     const float gi = (float)(gd[i] / norm);
@@ -788,10 +862,10 @@ __global__ void frame_prepare_kernel(const double* __restrict__ gd, uint64_t P, 
 // last sweep of the current frame back-projects instead of its own measurement, and the factor that converts the update
 // it produces into the next frame's normalisation. Saturated pixels stay negative (the norm is positive).
 __global__ void series_lookahead_kernel(const double* __restrict__ g_next, uint64_t P, const FrameScalars* cur,
-                                        const FrameScalars* next, float* __restrict__ g_spec, double* __restrict__ scale) {
+                                        const double* __restrict__ next_gmax, float* __restrict__ g_spec, double* __restrict__ scale) {
     const double norm = cur->norm;
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) *scale = norm / ((next->gmax > 0) ? next->gmax : 1.0);
+    if (i == 0) *scale = norm / ((*next_gmax > 0) ? *next_gmax : 1.0);
     if (i < P) g_spec[i] = (float)(g_next[i] / norm);
 }
 

@@ -18,8 +18,17 @@
 
 #include "sartsolver_b200.hpp"
 
+#ifdef SART_USE_REFERENCE_CONTAINERS
+// Test build (oracle/Makefile, where the reference's sources exist): the reference's OWN container classes, included from
+// where they lie; their HDF5-backed members are defined by oracle/ref_containers.cpp to fill from memory.
+#include "laplacian.hpp"
+#include "raytransfer.hpp"
+#include "ref_containers.hpp"
+#endif
+
 namespace {
 
+#ifndef SART_USE_REFERENCE_CONTAINERS
 // Stand-ins with the member names of the reference's containers (source/include/raytransfer.hpp:15-37,
 // source/include/laplacian.hpp:15-38): what SARTSolverB200's template constructor expects.
 class RayTransferMatrix {
@@ -44,6 +53,7 @@ public:
     const std::vector<float>& value() const { return val; }
     const std::vector<size_t>& index() const { return index1d; }
 };
+#endif
 
 template <typename T>
 bool read_n(FILE* f, T* dst, size_t n) {
@@ -67,13 +77,25 @@ int main(int argc, char** argv) {
     if (!read_n(f, hdr, 6) || !read_n(f, prm, 5)) return 1;
     const uint64_t npixel = hdr[0], nvoxel = hdr[1], nnz = hdr[2], nframes = hdr[3], flags = hdr[4];
     const int max_iterations = (int)hdr[5];
+    std::vector<double> frames(nframes * npixel), solution_vec;
+#ifdef SART_USE_REFERENCE_CONTAINERS
+    std::vector<float> matrix_src(npixel * nvoxel), lap_val(nnz);
+    std::vector<size_t> lap_idx(nnz);
+    bool ok = read_n(f, matrix_src.data(), npixel * nvoxel) && read_n(f, lap_idx.data(), nnz) &&
+              read_n(f, lap_val.data(), nnz) && read_n(f, frames.data(), nframes * npixel);
+    ref_containers_set_sources(matrix_src.data(), lap_idx.data(), lap_val.data(), nnz);
+    RayTransferMatrix raytransfer(npixel, nvoxel, 0);  // source/main.cpp:76-77
+    raytransfer.read_hdf5({}, "");
+    LaplacianMatrix laplacian(nnz ? nvoxel : 0);       // source/main.cpp:73-74
+    if (nnz) laplacian.read_hdf5("");
+#else
     RayTransferMatrix raytransfer(npixel, nvoxel, 0);
     LaplacianMatrix laplacian;
     laplacian.index1d.resize(nnz);
     laplacian.val.resize(nnz);
-    std::vector<double> frames(nframes * npixel), solution_vec;
     bool ok = read_n(f, raytransfer.storage().data(), npixel * nvoxel) && read_n(f, laplacian.index1d.data(), nnz) &&
               read_n(f, laplacian.val.data(), nnz) && read_n(f, frames.data(), nframes * npixel);
+#endif
     if (ok && (flags & 1)) {
         solution_vec.resize(nvoxel);
         ok = read_n(f, solution_vec.data(), nvoxel);

@@ -68,7 +68,7 @@ def test_unsorted_timeline_is_rejected(tmp_path):
     assert rc == 1 and "not sorted by time" in err
 
 
-@pytest.mark.parametrize("seed", range(12))
+@pytest.mark.parametrize("seed", range(40))
 def test_random_timelines_select_what_the_reference_selects(tmp_path, seed):
     """The driver's synchronisation (a search per grid point) against the restatement of the reference's own routine
     (oracle/timesync_oracle.py, source/image.cpp:83-196: it scatters every frame onto its grid point and the two
@@ -94,7 +94,7 @@ def test_random_timelines_select_what_the_reference_selects(tmp_path, seed):
     elif choice == 2:
         spec, intervals = "1:6,7.5:40:0.5", [(1.0, 6.0, 0.0, 0.0), (7.5, 40.0, 0.5, 0.0)]
     else:
-        spec, intervals = "0:50:2:2.5", [(0.0, 50.0, 2.0, 2.5)]
+        spec, intervals = "0:50:2:1.7", [(0.0, 50.0, 2.0, 1.7)]  # (the parser refuses a threshold above the step)
     want_idx, want_cam_t, want_t = composite_frames(timelines, intervals)
     rc, got = timesync(tmp_path, spec, *timelines)
     if not want_idx:

@@ -13,6 +13,9 @@ pytestmark = pytest.mark.gpu
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 DRIVER = os.path.join(ROOT, "mpi-cuda-sartsolver_b200", "host", "sart_b200_frames")
+# the same driver compiled against the reference's own RayTransferMatrix / LaplacianMatrix headers (oracle/Makefile; test
+# only, built where /root/reference exists and shipped to the GPU box with oracle/_ref/)
+DRIVER_REF_CONTAINERS = os.path.join(ROOT, "oracle", "_ref", "sart_b200_frames_refcontainers")
 
 
 def _write_problem(path, case):
@@ -56,6 +59,25 @@ def test_cpp_frame_loop_matches_golden(name, restatement, golden, tmp_path):
             assert abs(iters - git[f]) <= 1
             if iters == git[f]:
                 assert status == gst[f] and rel_l2(x, gx[f]) <= 1e-5
+
+
+@pytest.mark.parametrize("name", ["linear_masks_warmstart", "series_warm4"])
+def test_template_constructor_takes_the_reference_containers_as_they_are(name, restatement, tmp_path):
+    """SARTSolverB200's constructor is a template over the matrix containers; this driver instantiates it with the
+    reference's real classes (source/include/raytransfer.hpp:15-37, laplacian.hpp:15-38) and must give the very same bytes
+    as the build with the look-alike containers."""
+    if not os.path.exists(DRIVER_REF_CONTAINERS):
+        pytest.skip("oracle/_ref/sart_b200_frames_refcontainers not built (needs /root/reference at build time)")
+    case = build_case(name, restatement)
+    prob = tmp_path / "problem.bin"
+    _write_problem(prob, case)
+    sols = []
+    for exe in (DRIVER, DRIVER_REF_CONTAINERS):
+        sol = tmp_path / (os.path.basename(exe) + ".bin")
+        out = subprocess.run([exe, str(prob), str(sol)], capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr
+        sols.append(open(sol, "rb").read())
+    assert sols[0] == sols[1] and len(sols[0]) == case["frames"].shape[0] * (4 + 8 * case["H"].shape[1])
 
 
 def test_cpp_adaptor_rejects_bad_arguments_like_the_reference(tmp_path, restatement):
