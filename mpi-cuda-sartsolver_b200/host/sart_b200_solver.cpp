@@ -80,7 +80,6 @@ int main(int argc, char* argv[]) {
     std::vector<std::array<double, 4>> time_intervals;
     std::string error;
     if (!parse_time_intervals(config.time_range, time_intervals, error)) die(error);
-    if (config.use_cpu) die("This build has no CPU solver (--use_cpu): the engine runs on the GPU only.");
 
     // Inputs are either all HDF5 files in the reference's schemas (read with h5lite) or all flat stand-in files.
     const bool hdf5 = h5schema::is_hdf5(config.input_files.front());
@@ -149,6 +148,11 @@ int main(int argc, char* argv[]) {
     cfg.rank = rank;
     cfg.nranks = numproc;
     cfg.logarithmic = config.logarithmic ? 1 : 0;
+    // Which of the reference's two solvers this command line would have run decides the arithmetic where they differ
+    // observably (saturated pixels in the initial guess, the 1e-7 floor on the starting solution, the log solver's epsilon
+    // and penalty units): without --use_cpu the reference runs its CUDA solver (source/main.cpp:88-97),
+    // with it the CPU solver. Everything still runs on the GPU -- --use_cpu selects the CPU solver's semantics, not a CPU.
+    cfg.semantics = config.use_cpu ? SART_SEMANTICS_CPU : SART_SEMANTICS_GPU;
     cfg.ray_density_threshold = config.ray_density_threshold;  // source/main.cpp:105-110
     cfg.ray_length_threshold = config.ray_length_threshold;
     cfg.conv_tolerance = config.conv_tolerance;

@@ -84,7 +84,7 @@ def test_cpp_solver_driver_on_two_gpus(tmp_path):
     lap = tmp_path / "laplacian.h5"
     write_laplacian_h5(lap, case["lap"][0], case["lap"][1], V)
     out_path = tmp_path / "solution.h5"
-    argv = [EXE, "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]), "-l", str(lap),
+    argv = [EXE, "--use_cpu", "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]), "-l", str(lap),
             "-b", str(kw.get("beta_laplace", 2e-2)), *files]
     procs = []
     for rank in range(2):

@@ -40,7 +40,9 @@ def test_solver_cli_matches_golden(name, restatement, golden, tmp_path):
     kw = case["kw"]
     files = _write_inputs(tmp_path, case)
     out_path = tmp_path / "solution.bin"
-    argv = [EXE, "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]),
+    # --use_cpu: the golden vectors are the reference's CPU solver; without it the driver follows the GPU solver where the
+    # two differ (saturated pixels in the initial guess, the 1e-7 floor), as the reference's own default run does
+    argv = [EXE, "--use_cpu", "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]),
             "-R", str(kw.get("relaxation", 1.0))]
     if case["lap"] is not None:
         lap = tmp_path / "laplacian.lap"
@@ -75,10 +77,29 @@ def test_solver_cli_rejects_like_the_reference(tmp_path, restatement):
     files = _write_inputs(tmp_path, case)
     out = subprocess.run([EXE, "-R", "2", *files], capture_output=True, text=True)
     assert out.returncode == 1 and "relaxation must be within (0, 1] interval" in out.stderr
-    out = subprocess.run([EXE, "--use_cpu", *files], capture_output=True, text=True)
-    assert out.returncode == 1 and "no CPU solver" in out.stderr
     out = subprocess.run([EXE, files[0], files[1]], capture_output=True, text=True)  # an image file and one rtm block only
     assert out.returncode == 1
+
+
+def test_solver_cli_default_follows_the_gpu_solver_and_use_cpu_the_cpu_solver(tmp_path, restatement):
+    """The reference's default command line runs its CUDA solver, --use_cpu its CPU solver (source/main.cpp:88-97); where
+    the two differ observably -- here: saturated pixels in the default initial guess -- the driver follows the one the same
+    command line would have run."""
+    case = build_case("linear_masks_guess", restatement)
+    case["frames"] = case["frames"].copy()
+    case["frames"][:, ::13] = -1.0  # saturated pixels, no warm start
+    files = _write_inputs(tmp_path, case)
+    H, g = case["H"], case["frames"][0]
+    sols = {}
+    for flag in ("--use_cpu", None):
+        out_path = tmp_path / f"solution_{flag}.bin"
+        argv = [EXE] + ([flag] if flag else []) + ["-o", str(out_path), "-m", "3", "-c", "1e-30"]
+        out = subprocess.run(argv + files, capture_output=True, text=True, timeout=300)
+        assert out.returncode == 0, out.stderr
+        sols[flag] = read_solution(out_path)[0][3]
+        x_ref = restatement.solve(H, g, max_iterations=3, fixed_iterations=True, beta_laplace=0.0, gpu_semantics=flag is None)[0]
+        assert rel_l2(sols[flag], x_ref) <= 1e-5
+    assert rel_l2(sols[None], sols["--use_cpu"]) > 1e-4
 
 
 def _write_hdf5_inputs(tmp_path, case, rtm_name="with_reflections"):
@@ -118,7 +139,7 @@ def test_solver_cli_on_hdf5_files_matches_golden(name, restatement, golden, tmp_
     kw = case["kw"]
     files, times = _write_hdf5_inputs(tmp_path, case)
     out_path = tmp_path / "solution.h5"
-    argv = [EXE, "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]),
+    argv = [EXE, "--use_cpu", "-o", str(out_path), "-m", str(kw["max_iterations"]), "-c", repr(kw["conv_tolerance"]),
             "-R", str(kw.get("relaxation", 1.0)), "-n", "with_reflections"]
     V = case["H"].shape[1]
     if case["lap"] is not None:
