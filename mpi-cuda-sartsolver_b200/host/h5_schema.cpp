@@ -236,22 +236,21 @@ void read_laplacian(const std::string& path, uint64_t nvoxel, std::vector<uint64
     for (size_t q = 0; q < value.size(); ++q) flat_index[q] = i[q] * nvoxel + j[q];
 }
 
-void write_solution(const std::string& path, const std::vector<std::string>& camera_names, uint64_t nvoxel,
-                    const std::vector<double>& values, const std::vector<double>& time,
-                    const std::vector<std::vector<double>>& camera_time, const std::vector<int32_t>& status,
-                    const std::vector<int32_t>& iterations, const VoxelGrid& g) {
-    const uint64_t nframes = time.size();
-    h5lite::Writer w(path);
+// Solution::create_hdf5 (source/solution.cpp:60-112): every dataset of the "solution" group has an unlimited first
+// dimension; "value" is stored one frame per chunk, the one-dimensional ones in chunks of the first flush's length (here:
+// of max_cached_solutions frames). The voxel map goes in once, when the file is created (source/main.cpp:143-145 writes it
+// at the end; a file that is complete from the first flush on needs it then).
+SolutionFile::SolutionFile(const std::string& path, const std::vector<std::string>& camera_names, uint64_t nvoxel,
+                           uint64_t frames_per_flush, const VoxelGrid& g)
+    : writer(new h5lite::Writer(path)), cameras(camera_names), nvox(nvoxel) {
+    h5lite::Writer& w = *writer;
+    const uint64_t chunk = std::max<uint64_t>(frames_per_flush, 1);
     w.create_group("solution");
-    w.write_dataset("solution/value", {nframes, nvoxel}, values.data());
-    w.write_dataset("solution/time", {nframes}, time.data());
-    w.write_dataset("solution/status", {nframes}, status.data());
-    w.write_dataset("solution/iterations", {nframes}, iterations.data());  // not in the reference's file
-    for (size_t c = 0; c < camera_names.size(); ++c) {
-        std::vector<double> t(nframes);
-        for (uint64_t f = 0; f < nframes; ++f) t[f] = camera_time[f][c];
-        w.write_dataset("solution/time_" + camera_names[c], {nframes}, t.data());
-    }
+    w.create_extendible("solution/value", true, {nvoxel}, 1);
+    w.create_extendible("solution/time", true, {}, chunk);
+    w.create_extendible("solution/status", false, {}, chunk);
+    w.create_extendible("solution/iterations", false, {}, chunk);  // not in the reference's file
+    for (const auto& name : cameras) w.create_extendible("solution/time_" + name, true, {}, chunk);
     if (!g.voxmap.empty()) {  // source/voxelgrid.cpp:112-187
         w.create_group("voxel_map");
         w.set_attribute("voxel_map", "nx", g.nx);
@@ -279,7 +278,31 @@ void write_solution(const std::string& path, const std::vector<std::string>& cam
         w.write_dataset("voxel_map/k", {n}, k.data());
         w.write_dataset("voxel_map/value", {n}, value.data());
     }
-    w.close();
+    w.close();  // the file exists from now on, with zero frames
+}
+
+SolutionFile::~SolutionFile() { delete writer; }
+
+// Solution::update_hdf5 (source/solution.cpp:114-165): extend every dataset by the cached frames. After the call the file
+// on disk is complete up to and including these frames.
+void SolutionFile::append(const std::vector<double>& values, const std::vector<double>& time,
+                          const std::vector<std::vector<double>>& camera_time, const std::vector<int32_t>& status,
+                          const std::vector<int32_t>& iterations) {
+    const uint64_t n = time.size();
+    if (n == 0) return;
+    if (values.size() != n * nvox || status.size() != n || iterations.size() != n || camera_time.size() != n)
+        throw h5lite::Error("inconsistent solution cache");
+    h5lite::Writer& w = *writer;
+    w.append_rows("solution/value", values.data(), n);
+    w.append_rows("solution/time", time.data(), n);
+    w.append_rows("solution/status", status.data(), n);
+    w.append_rows("solution/iterations", iterations.data(), n);
+    for (size_t c = 0; c < cameras.size(); ++c) {
+        std::vector<double> t(n);
+        for (uint64_t f = 0; f < n; ++f) t[f] = camera_time[f][c];
+        w.append_rows("solution/time_" + cameras[c], t.data(), n);
+    }
+    w.flush();
 }
 
 }  // namespace h5schema

@@ -47,9 +47,23 @@ std::vector<float> read_block_rows(const RtmBlock& block, uint64_t row0, uint64_
 void read_laplacian(const std::string& path, uint64_t nvoxel, std::vector<uint64_t>& flat_index, std::vector<float>& value);
 
 // The reference's output file (source/solution.cpp:60-165, source/voxelgrid.cpp:112-187), written once.
-void write_solution(const std::string& path, const std::vector<std::string>& camera_names, uint64_t nvoxel,
-                    const std::vector<double>& values /* [nframes][nvoxel] */, const std::vector<double>& time,
-                    const std::vector<std::vector<double>>& camera_time /* [nframes][ncamera] */,
-                    const std::vector<int32_t>& status, const std::vector<int32_t>& iterations, const VoxelGrid& grid);
+// The reference's solution file (source/solution.cpp): created once, extended every few frames, complete on disk after
+// every append. Host memory holds only the frames since the last append.
+class SolutionFile {
+public:
+    SolutionFile(const std::string& path, const std::vector<std::string>& camera_names, uint64_t nvoxel,
+                 uint64_t frames_per_flush, const VoxelGrid& grid);
+    ~SolutionFile();
+    SolutionFile(const SolutionFile&) = delete;
+    SolutionFile& operator=(const SolutionFile&) = delete;
+    void append(const std::vector<double>& values /* [n][nvoxel] */, const std::vector<double>& time,
+                const std::vector<std::vector<double>>& camera_time /* [n][ncamera] */, const std::vector<int32_t>& status,
+                const std::vector<int32_t>& iterations);
+
+private:
+    h5lite::Writer* writer;
+    std::vector<std::string> cameras;
+    uint64_t nvox;
+};
 
 }  // namespace h5schema

@@ -596,12 +596,12 @@ Writer::Node::~Node() {
 Writer::Writer(const std::string& path) : filename(path) {}
 
 Writer::~Writer() {
-    if (!closed) {
-        try {
-            close();
-        } catch (...) {
-        }
+    try {
+        if (!closed) close();
+        flush();
+    } catch (...) {
     }
+    if (append_fp) std::fclose(append_fp);
 }
 
 Writer::Node* Writer::find(const std::string& path, bool parent_only, std::string* leaf) {
@@ -663,6 +663,141 @@ void Writer::write_dataset(const std::string& path, const std::vector<uint64_t>&
 }
 void Writer::write_dataset(const std::string& path, const std::vector<uint64_t>& dims, const uint64_t* data) {
     add_dataset(path, dims, type_integer(8, false), data, count_of(dims) * 8);
+}
+
+void Writer::create_extendible(const std::string& path, bool is_double, const std::vector<uint64_t>& row_shape, uint64_t chunk_rows) {
+    if (closed) throw Error("extendible datasets must be created before the file is laid out");
+    if (chunk_rows == 0) throw Error("chunk_rows must be positive");
+    std::string leaf;
+    Node* parent = find(path, true, &leaf);
+    if (leaf.empty() || !parent->is_group || parent->children.count(leaf)) throw Error("cannot create dataset " + path);
+    Node* n = new Node();
+    n->is_group = false;
+    n->extendible = true;
+    n->elem_size = is_double ? 8 : 4;
+    n->datatype = is_double ? type_float(8) : type_integer(4, true);
+    n->row_shape = row_shape;
+    n->chunk_rows = chunk_rows;
+    n->row_bytes = n->elem_size * count_of(row_shape);
+    const uint64_t chunk_bytes = n->row_bytes * chunk_rows;
+    if (chunk_bytes == 0 || chunk_bytes > 0xffffffffULL) throw Error("chunk of " + path + " is empty or larger than 4 GiB");
+    // dataspace message version 1 with maximum dimensions: the first one unlimited
+    std::vector<uint8_t> sp = {1, (uint8_t)(row_shape.size() + 1), 1, 0, 0, 0, 0, 0};
+    put<uint64_t>(sp, 0);
+    for (uint64_t d : row_shape) put<uint64_t>(sp, d);
+    put<uint64_t>(sp, kUndefined);
+    for (uint64_t d : row_shape) put<uint64_t>(sp, d);
+    n->dataspace = sp;
+    parent->children[leaf] = n;
+    extendibles.push_back(n);
+}
+
+void Writer::write_at(uint64_t address, const void* data, size_t bytes) {
+    if (!append_fp) {
+        append_fp = std::fopen(filename.c_str(), "r+b");
+        if (!append_fp) throw Error("cannot reopen " + filename + " for appending");
+    }
+    if (fseeko(append_fp, (off_t)address, SEEK_SET) != 0 || std::fwrite(data, 1, bytes, append_fp) != bytes)
+        throw Error("short write on " + filename);
+}
+
+void Writer::append_rows(const std::string& path, const void* rows, uint64_t nrows) {
+    Node* n = find(path, false, nullptr);
+    if (!n->extendible) throw Error(path + " is not an extendible dataset");
+    const uint8_t* src = static_cast<const uint8_t*>(rows);
+    if (!closed) {
+        n->pending.insert(n->pending.end(), src, src + nrows * n->row_bytes);
+        return;
+    }
+    append_to(n, src, nrows);
+}
+
+void Writer::append_to(Node* n, const uint8_t* src, uint64_t nrows) {
+    const uint64_t chunk_bytes = n->row_bytes * n->chunk_rows;
+    while (nrows) {
+        const uint64_t chunk = n->rows / n->chunk_rows, within = n->rows % n->chunk_rows;
+        if (chunk == n->chunk_address.size()) {  // a new chunk at the end of the file, fill value (0) behind the rows
+            const std::vector<uint8_t> zeros(chunk_bytes, 0);
+            n->chunk_address.push_back(eof);
+            write_at(eof, zeros.data(), zeros.size());
+            eof += chunk_bytes;
+        }
+        const uint64_t take = std::min(nrows, n->chunk_rows - within);
+        write_at(n->chunk_address[chunk] + within * n->row_bytes, src, take * n->row_bytes);
+        src += take * n->row_bytes;
+        n->rows += take;
+        nrows -= take;
+        n->dirty = true;
+    }
+}
+
+// Version-1 B-tree of node type 1 over the dataset's chunks, written at the end of the file; returns the root's address.
+// Key: chunk size in bytes, filter mask, the chunk's offset in every dimension plus one zero for the element; a node
+// holds up to 64 children (the default "indexed storage" rank of superblock version 0) and is allocated at full size,
+// as the library reads it; the last key of a node bounds its last child from above.
+uint64_t Writer::write_chunk_index(Node* n) {
+    constexpr size_t kFan = 64;
+    const size_t rank = n->row_shape.size() + 1;
+    const size_t key_bytes = 8 + 8 * (rank + 1);
+    const size_t node_bytes = 24 + kFan * (key_bytes + 8) + key_bytes;
+    const uint32_t chunk_bytes = (uint32_t)(n->row_bytes * n->chunk_rows);
+    auto key_of = [&](uint64_t first_row, std::vector<uint8_t>& out) {
+        put<uint32_t>(out, chunk_bytes);
+        put<uint32_t>(out, 0);
+        put<uint64_t>(out, first_row);
+        for (size_t k = 1; k <= rank; ++k) put<uint64_t>(out, 0);  // other dimensions start at 0; the element entry is 0
+    };
+    struct Entry {
+        uint64_t first_row, address;
+    };
+    std::vector<Entry> level_entries;
+    for (size_t c = 0; c < n->chunk_address.size(); ++c) level_entries.push_back({c * n->chunk_rows, n->chunk_address[c]});
+    const uint64_t end_row = n->chunk_address.size() * n->chunk_rows;
+    int level = 0;
+    while (true) {
+        const size_t nnodes = std::max<size_t>(1, (level_entries.size() + kFan - 1) / kFan);
+        std::vector<Entry> parents;
+        const uint64_t first_node = eof;
+        for (size_t b = 0; b < nnodes; ++b) {
+            const size_t lo = b * kFan, hi = std::min(level_entries.size(), lo + kFan);
+            std::vector<uint8_t> node;
+            put_bytes(node, "TREE", 4);
+            node.push_back(1);
+            node.push_back((uint8_t)level);
+            put<uint16_t>(node, (uint16_t)(hi - lo));
+            put<uint64_t>(node, b ? first_node + (b - 1) * node_bytes : kUndefined);              // left sibling
+            put<uint64_t>(node, b + 1 < nnodes ? first_node + (b + 1) * node_bytes : kUndefined);  // right sibling
+            for (size_t i = lo; i < hi; ++i) {
+                key_of(level_entries[i].first_row, node);
+                put<uint64_t>(node, level_entries[i].address);
+            }
+            key_of(hi < level_entries.size() ? level_entries[hi].first_row : end_row, node);
+            node.resize(node_bytes, 0);
+            write_at(eof, node.data(), node.size());
+            parents.push_back({lo < level_entries.size() ? level_entries[lo].first_row : 0, eof});
+            eof += node_bytes;
+        }
+        if (nnodes == 1) return first_node;
+        level_entries.swap(parents);
+        ++level;
+    }
+}
+
+void Writer::flush() {
+    if (!closed) return;
+    bool any = false;
+    for (Node* n : extendibles) {
+        if (!n->dirty) continue;
+        const uint64_t root_node = write_chunk_index(n);
+        write_at(n->index_field, &root_node, 8);
+        write_at(n->extent_field, &n->rows, 8);
+        n->dirty = false;
+        any = true;
+    }
+    if (any) {
+        write_at(40, &eof, 8);  // end-of-file address of the superblock
+        std::fflush(append_fp);
+    }
 }
 
 void Writer::add_attribute(const std::string& object_path, const std::string& name, const std::vector<uint8_t>& datatype,
@@ -733,6 +868,11 @@ void Writer::close() {
             cursor += n->data_bytes;
             n->snod = cursor;
             cursor += 8 + 2 * kLeafK * 40;
+        } else if (n->extendible) {
+            // dataspace, datatype, fill value (version 2 with the value), chunked layout (version 3)
+            const uint64_t fill = 8 + pad8(8 + n->elem_size), layout = 8 + pad8(3 + 8 + 4 * (n->row_shape.size() + 2));
+            cursor += 16 + (8 + pad8(n->dataspace.size())) + (8 + pad8(n->datatype.size())) + fill + layout + attr_bytes(n);
+            cursor = pad8(cursor);
         } else {
             cursor += 16 + (8 + pad8(n->dataspace.size())) + (8 + pad8(n->datatype.size())) + (8 + 8) /*fill*/ + (8 + 24) /*layout*/ + attr_bytes(n);
             cursor = pad8(cursor);
@@ -740,7 +880,7 @@ void Writer::close() {
             cursor += pad8(n->owned.size());
         }
     }
-    const uint64_t eof = cursor;
+    eof = cursor;
 
     std::vector<uint8_t> f(eof, 0);
     auto at = [&](uint64_t a) { return f.data() + a; };
@@ -774,6 +914,21 @@ void Writer::close() {
             put<uint64_t>(st, n->btree);
             put<uint64_t>(st, n->heap);
             append_message(msgs, 0x0011, st);
+        } else if (n->extendible) {
+            n->extent_field = n->header_address + 16 + msgs.size() + 8 + 8;  // dims[0] inside the dataspace message
+            append_message(msgs, 0x0001, n->dataspace);
+            append_message(msgs, 0x0003, n->datatype, 1);
+            std::vector<uint8_t> fill = {2, 3, 2, 1};  // version 2: allocate incrementally, write if set, value defined (0)
+            put<uint32_t>(fill, n->elem_size);
+            fill.resize(fill.size() + n->elem_size, 0);
+            append_message(msgs, 0x0005, fill);
+            n->index_field = n->header_address + 16 + msgs.size() + 8 + 3;  // B-tree address inside the layout message
+            std::vector<uint8_t> lay = {3, 2, (uint8_t)(n->row_shape.size() + 2)};
+            put<uint64_t>(lay, kUndefined);  // no chunk yet
+            put<uint32_t>(lay, (uint32_t)n->chunk_rows);
+            for (uint64_t d : n->row_shape) put<uint32_t>(lay, (uint32_t)d);
+            put<uint32_t>(lay, n->elem_size);
+            append_message(msgs, 0x0008, lay);
         } else {
             append_message(msgs, 0x0001, n->dataspace);
             append_message(msgs, 0x0003, n->datatype, 1);
@@ -793,7 +948,7 @@ void Writer::close() {
         store(n->header_address + 16, msgs);
 
         if (!n->is_group) {
-            store(n->data_address, n->owned);
+            if (!n->extendible) store(n->data_address, n->owned);
             continue;
         }
         // local heap: names sorted (std::map order == strcmp order for plain ASCII)
@@ -861,6 +1016,14 @@ void Writer::close() {
     const bool ok = std::fwrite(f.data(), 1, f.size(), out) == f.size();
     std::fclose(out);
     if (!ok) throw Error("short write on " + filename);
+    // rows appended before the file existed
+    for (Node* n : extendibles) {
+        if (n->pending.empty()) continue;
+        std::vector<uint8_t> rows;
+        rows.swap(n->pending);
+        append_to(n, rows.data(), rows.size() / n->row_bytes);
+    }
+    flush();
 }
 
 }  // namespace h5lite

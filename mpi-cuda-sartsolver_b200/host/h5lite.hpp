@@ -10,8 +10,11 @@
 //   (libver "earliest"); files made with libver "latest" (version-2 object headers, fractal heaps) are rejected with a
 //   clear message.
 // Writer: superblock 0, old-style groups (one symbol node per group, up to 64 links), contiguous datasets, version-1
-//   attribute messages, fixed-length strings: enough for the reference's output file (source/solution.cpp,
-//   source/voxelgrid.cpp:112-187) written once at the end of the run instead of in extendible chunks.
+//   attribute messages, fixed-length strings, and EXTENDIBLE datasets: chunked layout (version-3 layout message, version-1
+//   chunk B-tree), first dimension unlimited, rows appended after the file has been laid out -- what the reference's
+//   solution file is (source/solution.cpp:60-165: created with H5S_UNLIMITED, extended every max_cached_solutions frames).
+//   An append writes the new chunks and a fresh chunk index at the end of the file, then updates three fixed-size fields
+//   (dataset extent, index address, end-of-file address), so the file is a complete HDF5 file after every flush.
 #pragma once
 
 #include <cstdint>
@@ -123,7 +126,14 @@ public:
     void set_attribute(const std::string& object_path, const std::string& name, uint64_t value);
     void set_attribute(const std::string& object_path, const std::string& name, int32_t value);
     void set_attribute(const std::string& object_path, const std::string& name, const std::string& value);
-    void close();  // lays the file out and writes it; called by the destructor if not called before
+    // Extendible dataset of doubles (is_double) or 32-bit signed integers: dims {0, row_shape...}, maximum dims
+    // {unlimited, row_shape...}, chunks of chunk_rows rows. Rows are added with append_rows() -- before close() they are
+    // buffered and written with the file, after close() they go to the end of the file; flush() makes them part of the
+    // dataset (new chunk index, new extent). Reference: Solution::create_hdf5 / update_hdf5, source/solution.cpp:60-165.
+    void create_extendible(const std::string& path, bool is_double, const std::vector<uint64_t>& row_shape, uint64_t chunk_rows);
+    void append_rows(const std::string& path, const void* rows, uint64_t nrows);
+    void flush();
+    void close();  // lays the file out and writes it (extendible datasets stay open for append_rows / flush)
 
 private:
     struct Node {
@@ -135,8 +145,23 @@ private:
         std::vector<uint8_t> owned;
         uint64_t data_bytes = 0;
         uint64_t header_address = 0, btree = 0, heap = 0, heap_data = 0, snod = 0, data_address = 0;
+        // extendible datasets
+        bool extendible = false;
+        std::vector<uint64_t> row_shape;
+        uint64_t chunk_rows = 0, row_bytes = 0, rows = 0;         // rows = current extent of the first dimension
+        uint32_t elem_size = 0;
+        std::vector<uint8_t> pending;                              // rows appended before close()
+        std::vector<uint64_t> chunk_address;                       // chunk k holds rows [k * chunk_rows, (k + 1) * chunk_rows)
+        uint64_t extent_field = 0, index_field = 0;                // file offsets of dims[0] and of the B-tree address
+        bool dirty = false;
         ~Node();
     };
+    FILE* append_fp = nullptr;
+    uint64_t eof = 0;
+    std::vector<Node*> extendibles;
+    void write_at(uint64_t address, const void* data, size_t bytes);
+    uint64_t write_chunk_index(Node* n);
+    void append_to(Node* n, const uint8_t* rows, uint64_t nrows);
     std::string filename;
     Node root;
     bool closed = false;

@@ -56,6 +56,15 @@ int h5w_attr_i32(void* w, const char* obj, const char* name, int32_t v) {
 int h5w_attr_str(void* w, const char* obj, const char* name, const char* v) {
     return guard([&] { static_cast<h5lite::Writer*>(w)->set_attribute(obj, name, std::string(v)); });
 }
+// extendible datasets (rows appended before or after h5w_layout; h5w_flush makes appended rows part of the dataset)
+int h5w_extendible(void* w, const char* path, int is_double, const uint64_t* row_shape, int row_rank, uint64_t chunk_rows) {
+    return guard([&] { static_cast<h5lite::Writer*>(w)->create_extendible(path, is_double != 0, dims_of(row_shape, row_rank), chunk_rows); });
+}
+int h5w_append(void* w, const char* path, const void* rows, uint64_t nrows) {
+    return guard([&] { static_cast<h5lite::Writer*>(w)->append_rows(path, rows, nrows); });
+}
+int h5w_layout(void* w) { return guard([&] { static_cast<h5lite::Writer*>(w)->close(); }); }
+int h5w_flush(void* w) { return guard([&] { static_cast<h5lite::Writer*>(w)->flush(); }); }
 int h5w_close(void* w) {
     const int rc = guard([&] { static_cast<h5lite::Writer*>(w)->close(); });
     delete static_cast<h5lite::Writer*>(w);

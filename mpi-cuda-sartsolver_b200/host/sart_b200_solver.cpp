@@ -258,16 +258,25 @@ int main(int argc, char* argv[]) {
             std::fwrite(x, sizeof(double), nvoxel, out);
         }
     };
+    h5schema::SolutionFile* h5_file = nullptr;
     auto flush = [&](size_t done) {
-        // source/solution.cpp:55, 167-180: the reference appends to the file every max_cached_solutions frames so that a
-        // long run leaves its results behind if it dies; with a write-once container the file is rewritten instead
-        if (!(h5_out && rank == 0) || done >= frames->size() || done % (size_t)config.max_cached_solutions != 0) return;
+        // source/solution.cpp:55, 114-180: the cached solutions are appended to the file every max_cached_solutions frames
+        // (and at the end), so a long run keeps at most that many in host memory and leaves a complete file behind
+        // whenever it stops
+        if (!(h5_out && rank == 0) || all_time.empty()) return;
+        if (done < frames->size() && all_time.size() < (size_t)config.max_cached_solutions) return;
         try {
-            h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time, all_status,
-                                     all_iterations, h5.grid);
+            if (!h5_file)
+                h5_file = new h5schema::SolutionFile(config.output_file, camera_names, nvoxel, (uint64_t)config.max_cached_solutions, h5.grid);
+            h5_file->append(all_values, all_time, all_camera_time, all_status, all_iterations);
         } catch (const std::exception& err) {
             die(err.what());
         }
+        all_values.clear();
+        all_time.clear();
+        all_camera_time.clear();
+        all_status.clear();
+        all_iterations.clear();
     };
     std::vector<double> solution_vec, frame;
     size_t k = 0;
@@ -326,12 +335,8 @@ int main(int argc, char* argv[]) {
         k += nb;
     }
     if (h5_out && rank == 0) {
-        try {
-            h5schema::write_solution(config.output_file, camera_names, nvoxel, all_values, all_time, all_camera_time, all_status,
-                                     all_iterations, h5.grid);
-        } catch (const std::exception& err) {
-            die(err.what());
-        }
+        flush(frames->size());
+        delete h5_file;
     } else if (out) {
         std::fclose(out);
     }

@@ -33,6 +33,10 @@ def _capi():
         L.h5w_attr_i32.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int32]
         L.h5w_attr_str.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p]
         L.h5w_close.argtypes = [C.c_void_p]
+        L.h5w_extendible.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_void_p, C.c_int, C.c_uint64]
+        L.h5w_append.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_uint64]
+        L.h5w_layout.argtypes = [C.c_void_p]
+        L.h5w_flush.argtypes = [C.c_void_p]
         L.h5w_open.argtypes = [C.c_char_p]
         _lib = L
     return _lib
@@ -67,6 +71,23 @@ class H5Writer:
             self._ok(self.L.h5w_attr_i32(self.h, obj.encode(), name.encode(), int(value)))
         else:
             self._ok(self.L.h5w_attr_u64(self.h, obj.encode(), name.encode(), int(value)))
+
+    def extendible(self, path, dtype, row_shape, chunk_rows):
+        """Dataset with an unlimited first dimension (float64 or int32 rows of ``row_shape``), chunks of ``chunk_rows`` rows."""
+        shape = (C.c_uint64 * max(len(row_shape), 1))(*row_shape)
+        self._ok(self.L.h5w_extendible(self.h, path.encode(), int(np.dtype(dtype) == np.float64), shape, len(row_shape), chunk_rows))
+
+    def append(self, path, rows):
+        a = np.ascontiguousarray(rows)
+        assert a.dtype in (np.float64, np.int32)
+        self._ok(self.L.h5w_append(self.h, path.encode(), a.ctypes.data_as(C.c_void_p), a.shape[0]))
+
+    def layout(self):
+        """Writes the file; extendible datasets stay open for append() / flush()."""
+        self._ok(self.L.h5w_layout(self.h))
+
+    def flush(self):
+        self._ok(self.L.h5w_flush(self.h))
 
     def close(self):
         self._ok(self.L.h5w_close(self.h))

@@ -78,3 +78,54 @@ def test_rejects_what_it_cannot_read(tmp_path):
     p.write_bytes(bytes(v2))
     out = subprocess.run([os.path.join(HOST, "sart_b200_h5ls"), str(p)], capture_output=True, text=True)
     assert out.returncode == 1 and "not supported" in out.stderr
+
+
+def test_extendible_datasets_grow_flush_by_flush(tmp_path):
+    """The solution file's shape (source/solution.cpp:60-165): datasets with an unlimited first dimension, extended every
+    few frames. After EVERY flush the file on disk must be a complete file holding exactly the rows flushed so far --
+    through a chunk index of one, two and three levels (64 children per node), one-row chunks for the 2-D dataset and
+    a partly filled last chunk for the 1-D ones -- next to ordinary datasets and attributes written at lay-out time."""
+    p = tmp_path / "grow.h5"
+    rng = np.random.default_rng(3)
+    nvox = 11
+    w = H5Writer(p)
+    w.group("solution")
+    w.attr("solution", "nvoxel", nvox)
+    w.dataset("solution/fixed", np.arange(6, dtype=np.float64).reshape(2, 3))
+    w.extendible("solution/value", np.float64, (nvox,), 1)
+    w.extendible("solution/time", np.float64, (), 7)
+    w.extendible("solution/status", np.int32, (), 7)
+    value = rng.standard_normal((3, nvox))
+    time_ = np.arange(3, dtype=np.float64)
+    status = np.array([0, -1, 0], dtype=np.int32)
+    w.append("solution/value", value)   # rows buffered before the file exists
+    w.append("solution/time", time_)
+    w.append("solution/status", status)
+    w.layout()
+
+    def check():
+        o = h5ls(p)
+        n = len(time_)
+        assert o["solution/value"]["dims"] == [n, nvox] and o["solution/value"]["layout"] == 2
+        np.testing.assert_array_equal(np.array(o["solution/value"]["values"]).reshape(n, nvox), value)
+        np.testing.assert_array_equal(o["solution/time"]["values"], time_)
+        assert o["solution/status"]["values"] == status.tolist()
+        assert o["solution/fixed"]["values"] == [0.0, 1.0, 2.0, 3.0, 4.0, 5.0] and o["solution"]["attributes"] == {"nvoxel": nvox}
+        assert os.path.getsize(p) >= 96
+
+    import os
+    check()
+    for batch in (2, 5, 60, 1, 70, 4100):  # 3 -> 5 -> 10 -> 70 (two index levels) -> 71 -> 141 -> 4241 rows (three levels)
+        v = rng.standard_normal((batch, nvox))
+        t = len(time_) + np.arange(batch, dtype=np.float64)
+        s = rng.integers(-1, 1, batch).astype(np.int32)
+        w.append("solution/value", v)
+        w.append("solution/time", t)
+        w.append("solution/status", s)
+        before = h5ls(p, values=False)["solution/value"]["dims"][0]
+        assert before == len(time_)  # appended rows do not show before the flush
+        w.flush()
+        value, time_, status = np.vstack([value, v]), np.concatenate([time_, t]), np.concatenate([status, s])
+        check()
+    w.close()
+    check()
