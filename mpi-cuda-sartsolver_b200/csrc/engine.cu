@@ -1342,10 +1342,15 @@ int setup_peer_exchange(sart_engine* e) {
     // a buffer holds V + 1 doubles (per-sweep kernels) or one record [sum(fit^2)][chunk] per CTA (whole-solve kernel)
     const uint64_t nblk = std::max<uint64_t>((uint64_t)e->fu_cluster * (e->persistent ? e->fs_nclusters : e->fu_nclusters), 1);
     const uint64_t rank_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kFlagStride, 256) * 256;
-    const uint64_t cta_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * nblk * 8, 256) * 256;
+    // The layout must be the same on every rank (a rank addresses its peers' regions with its own offsets), but the grid
+    // is not always: ranks whose shards differ by a row can plan one cluster more or less on tiny problems. So the
+    // regions are laid out for the largest grid any rank could run, not for this rank's own.
+    constexpr uint64_t kLayoutCtas = 4096;  // >= 16 CTAs per cluster x resident clusters on any device
+    if (nblk > kLayoutCtas) ok = 0;
+    const uint64_t cta_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kLayoutCtas * 8, 256) * 256;
     const uint64_t stat_slots_bytes = ceil_div((uint64_t)kStatSlots * sizeof(StatPair), 256) * 256;
     const uint64_t flags_bytes = rank_flags_bytes + cta_flags_bytes + rank_flags_bytes + 2 * stat_slots_bytes;
-    const uint64_t buf_bytes = ceil_div((e->V + 2 * nblk + 2) * sizeof(double), 256) * 256;
+    const uint64_t buf_bytes = ceil_div((e->V + 2 * kLayoutCtas + 2) * sizeof(double), 256) * 256;
     e->xchg_cta_flag_off = rank_flags_bytes;
     e->xchg_stat_flag_off = rank_flags_bytes + cta_flags_bytes;
     e->xchg_stat_slot_off[0] = e->xchg_stat_flag_off + rank_flags_bytes;
