@@ -29,6 +29,26 @@ CameraSeries camera_from_raw(const rawfiles::ImgHeader& h) {
         if (!ok) error = "short read on " + path;
         return ok;
     };
+    // consecutive frames are consecutive in the file: whole-camera reads of a run are one contiguous read
+    c.read_run = [path, data_offset, npixel](size_t index, size_t nframes, uint64_t first, uint64_t count, double* out,
+                                             uint64_t out_stride, std::string& error) {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) {
+            error = "cannot open " + path;
+            return false;
+        }
+        bool ok = true;
+        if (count == npixel && out_stride == npixel) {
+            ok = fseeko(f, (off_t)(data_offset + index * npixel * 8), SEEK_SET) == 0 && rawfiles::read_exact(f, out, nframes * npixel * 8);
+        } else {
+            for (size_t k = 0; k < nframes && ok; ++k)
+                ok = fseeko(f, (off_t)(data_offset + ((index + k) * npixel + first) * 8), SEEK_SET) == 0 &&
+                     rawfiles::read_exact(f, out + k * out_stride, count * 8);
+        }
+        std::fclose(f);
+        if (!ok) error = "short read on " + path;
+        return ok;
+    };
     return c;
 }
 
@@ -154,5 +174,36 @@ bool CompositeFrames::read(size_t k, uint64_t offset, uint64_t count, std::vecto
         if (lo >= hi) continue;
         if (!im.read(frame_indices[k][cam], lo - im.pixel_offset, hi - lo, out.data() + (lo - offset), error)) return false;
     }
+    return true;
+}
+
+bool CompositeFrames::read_chunk(size_t k0, size_t n, uint64_t offset, uint64_t count, std::vector<double>& out, std::string& error,
+                                 size_t* reads) const {
+    out.assign(n * count, 0.0);
+    size_t issued = 0;
+    for (size_t cam = 0; cam < images.size(); ++cam) {
+        const auto& im = images[cam];
+        const uint64_t lo = std::max(offset, im.pixel_offset), hi = std::min(offset + count, im.pixel_offset + im.npixel);
+        if (lo >= hi) continue;
+        double* dst = out.data() + (lo - offset);
+        size_t b = 0;
+        while (b < n) {
+            // the longest run of composite frames whose frames of this camera follow each other in its file
+            size_t e = b + 1;
+            while (e < n && frame_indices[k0 + e][cam] == frame_indices[k0 + e - 1][cam] + 1) ++e;
+            const size_t first_index = frame_indices[k0 + b][cam];
+            if (im.read_run) {
+                if (!im.read_run(first_index, e - b, lo - im.pixel_offset, hi - lo, dst + b * count, count, error)) return false;
+                ++issued;
+            } else {
+                for (size_t k = b; k < e; ++k) {
+                    if (!im.read(frame_indices[k0 + k][cam], lo - im.pixel_offset, hi - lo, dst + k * count, error)) return false;
+                    ++issued;
+                }
+            }
+            b = e;
+        }
+    }
+    if (reads) *reads = issued;
     return true;
 }

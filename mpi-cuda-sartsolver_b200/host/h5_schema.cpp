@@ -205,6 +205,20 @@ Problem open_problem(const std::vector<std::string>& input_files, const std::str
             }
             return true;
         };
+        // a run of consecutive frames: one read of the dataset's rows [index, index + nframes), then the mask per frame
+        c.read_run = [file, selected](size_t index, size_t nframes, uint64_t first, uint64_t count, double* out, uint64_t out_stride,
+                                      std::string& error) {
+            try {
+                const std::vector<double> block = file->read_rows<double>("image/frame", index, nframes);
+                const uint64_t frame_elems = block.size() / nframes;
+                for (size_t k = 0; k < nframes; ++k)
+                    for (uint64_t q = 0; q < count; ++q) out[k * out_stride + q] = block[k * frame_elems + (*selected)[first + q]];
+            } catch (const std::exception& err) {
+                error = err.what();
+                return false;
+            }
+            return true;
+        };
         pb.cameras.push_back(std::move(c));
         pb.camera_names.push_back(cam.first);
         offset += r.npixel;

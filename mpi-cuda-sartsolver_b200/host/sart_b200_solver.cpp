@@ -283,11 +283,8 @@ int main(int argc, char* argv[]) {
     while (k < frames->size()) {
         const size_t nb = config.no_guess ? std::min<size_t>(4, frames->size() - k) : 1;
         if (nb >= 2) {
-            std::vector<double> group_frames(nb * npixel_local), group_solutions(nb * nvoxel), one;
-            for (size_t b = 0; b < nb; ++b) {
-                if (!frames->read(k + b, offset_pixel, npixel_local, one, error)) die(error);
-                std::copy(one.begin(), one.end(), group_frames.begin() + b * npixel_local);
-            }
+            std::vector<double> group_frames, group_solutions(nb * nvoxel);
+            if (!frames->read_chunk(k, nb, offset_pixel, npixel_local, group_frames, error)) die(error);
             const auto last = std::chrono::steady_clock::now();
             std::vector<int32_t> status(nb, 0), iterations(nb, 0);
             must(sart_solve_batch(engine, (int32_t)nb, group_frames.data(), group_solutions.data(), status.data(), iterations.data()));
@@ -301,11 +298,9 @@ int main(int argc, char* argv[]) {
             // warm-started frames in chunks of max_cached_frames (the reference's frame cache, source/image.cpp:268-331):
             // sart_solve_series knows the next frame while it solves the current one
             const size_t nc = std::min<size_t>((size_t)config.max_cached_frames, frames->size() - k);
-            std::vector<double> chunk(nc * npixel_local), chunk_solutions(nc * nvoxel), one;
-            for (size_t b = 0; b < nc; ++b) {
-                if (!frames->read(k + b, offset_pixel, npixel_local, one, error)) die(error);
-                std::copy(one.begin(), one.end(), chunk.begin() + b * npixel_local);
-            }
+            // (one read per camera and run of consecutive frames, like the reference's cache refill)
+            std::vector<double> chunk, chunk_solutions(nc * nvoxel);
+            if (!frames->read_chunk(k, nc, offset_pixel, npixel_local, chunk, error)) die(error);
             const auto last = std::chrono::steady_clock::now();
             std::vector<int32_t> status(nc, 0), iterations(nc, 0);
             must(sart_solve_series(engine, (int32_t)nc, chunk.data(), solution_vec.empty() ? nullptr : solution_vec.data(),

@@ -104,3 +104,32 @@ def test_random_timelines_select_what_the_reference_selects(tmp_path, seed):
     assert [f["indices"] for f in got] == want_idx
     assert np.allclose([f["time"] for f in got], want_t, rtol=0, atol=1e-9)
     assert np.allclose([f["camera_time"] for f in got], want_cam_t, rtol=0, atol=1e-9)
+
+
+def test_chunk_reads_fetch_runs_of_frames_in_one_go(tmp_path):
+    """The frame cache of the reference (source/image.cpp:268-331) as the driver has it: the frames of a chunk come in with
+    one read per camera and run of consecutive frame indices, and hold exactly what frame-by-frame reads give -- whole
+    frames and a rank's pixel window alike."""
+    rng = np.random.default_rng(7)
+    t0 = [0.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0]
+    t1 = [0.0, 0.5, 1.0, 1.5, 2.0, 2.5, 3.0, 3.5, 4.0, 4.5, 5.0, 5.5, 6.0, 6.5, 7.0]  # twice as fast: every other frame is used
+    paths, off = [], 0
+    for c, times in enumerate((t0, t1)):
+        p = tmp_path / f"cam{c}.img"
+        write_img(p, rng.random((len(times), 5)), times, off)
+        off += 5
+        paths.append(str(p))
+    if not os.path.exists(EXE):
+        subprocess.check_call(["make", "-C", os.path.dirname(EXE), "sart_b200_timesync"])
+    for window in (None, "3:4"):
+        env = dict(os.environ, SART_TIMESYNC_CHUNK="4")
+        if window:
+            env["SART_TIMESYNC_WINDOW"] = window
+        out = subprocess.run([EXE, "", *paths], capture_output=True, text=True, env=env)
+        assert out.returncode == 0, out.stderr
+        lines = [json.loads(l) for l in out.stdout.splitlines()]
+        frames, summary = lines[:-1], lines[-1]
+        assert [f["indices"] for f in frames] == [[k, 2 * k] for k in range(8)]
+        assert summary["equal"] == 1 and summary["checksum"] > 0
+        # camera 0: one run per chunk of four frames; camera 1 uses every other frame: no runs, one read per frame
+        assert summary["chunk_reads"] == 2 * 1 + 2 * 4 and summary["frame_reads"] == 16
