@@ -105,9 +105,16 @@ File::File(const std::string& path) : filename(path) {
     uint8_t sb[96];
     read_at(0, sb, 8 + 48);
     const int version = sb[8];
-    if (version > 1)
-        throw Error(path + ": superblock version " + std::to_string(version) +
-                    " (libver 'latest' files) is not supported by this reader");
+    if (version == 2 || version == 3) {
+        // superblock versions 2 / 3 (libver "latest"): sizes of offsets / lengths, flags, base address, superblock extension,
+        // end of file, root group OBJECT HEADER address, checksum
+        if (sb[9] != 8 || sb[10] != 8) throw Error(path + ": only 8-byte offsets and lengths are supported");
+        const uint64_t base_address = get<uint64_t>(sb + 12);
+        if (base_address != 0 && base_address != base) base = base_address;
+        root_header = get<uint64_t>(sb + 36);
+        return;
+    }
+    if (version > 3) throw Error(path + ": superblock version " + std::to_string(version) + " is not supported by this reader");
     if (sb[13] != 8 || sb[14] != 8) throw Error(path + ": only 8-byte offsets and lengths are supported");
     // v0: 24 bytes of fixed fields, v1 has 4 more (indexed storage K + reserved)
     const size_t fixed = (version == 0) ? 24 : 28;
