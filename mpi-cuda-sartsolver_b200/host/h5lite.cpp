@@ -275,6 +275,42 @@ void File::parse_messages(const std::vector<uint8_t>& block, Object& obj, std::v
                     } else if (d.layout == 2) {
                         for (int i = 0; i + 1 < rank; ++i) d.chunk_dims.push_back(dims[i]);
                     }
+                } else if (version == 4) {
+                    // layout version 4 (libver "latest"): compact and contiguous as in version 3; chunked: flags,
+                    // dimensionality, width of a dimension size, the sizes (the last one is the element size), the kind of
+                    // chunk index with its parameters, the index's address
+                    d.layout = body[1];
+                    if (d.layout == 0) {
+                        const uint16_t n = get<uint16_t>(body + 2);
+                        d.compact.assign(body + 4, body + 4 + n);
+                    } else if (d.layout == 1) {
+                        d.address = get<uint64_t>(body + 2);
+                        d.storage_size = get<uint64_t>(body + 10);
+                    } else if (d.layout == 2) {
+                        const uint8_t cflags = body[2];
+                        const int rank = body[3], enc = body[4];
+                        size_t off = 5;
+                        for (int i = 0; i < rank; ++i, off += enc) {
+                            uint64_t v = 0;
+                            std::memcpy(&v, body + off, enc);
+                            if (i + 1 < rank) d.chunk_dims.push_back(v);
+                        }
+                        d.chunk_index = body[off++];
+                        if (d.chunk_index == 1) {  // a single chunk
+                            if (cflags & 2) {
+                                d.single_chunk_size = get<uint64_t>(body + off);
+                                d.single_filter_mask = get<uint32_t>(body + off + 8);
+                                off += 12;
+                            }
+                        } else if (d.chunk_index == 2) {  // implicit: all chunks allocated, in order, no filters
+                        } else if (d.chunk_index == 3) {  // fixed array
+                            off += 1;                      // page bits
+                        } else {
+                            throw Error(filename + ": chunk index type " + std::to_string(d.chunk_index) +
+                                        " (extensible array / version-2 B-tree) is not supported by this reader");
+                        }
+                        d.address = get<uint64_t>(body + off);
+                    } else throw Error("unsupported data layout class");
                 } else throw Error("data layout message version " + std::to_string(version) + " is not supported");
                 break;
             }
@@ -318,9 +354,36 @@ void File::parse_messages(const std::vector<uint8_t>& block, Object& obj, std::v
                 walk_group_btree(btree, get<uint64_t>(h + 24), obj.links);
                 break;
             }
-            case 0x0002:
-            case 0x0006:
-                throw Error(filename + " uses new-style groups (libver 'latest'), which this reader does not support");
+            case 0x0002: {
+                // link info (new-style group): version, flags, [max creation index], fractal heap address, name index address.
+                // The links of a small group are link messages in the header ("compact"); a defined heap address means
+                // "dense" storage (fractal heap + version-2 B-tree), which this reader does not follow.
+                obj.is_group = true;
+                const size_t off = 2 + ((body[1] & 1) ? 8 : 0);
+                if (size >= off + 8 && get<uint64_t>(body + off) != kUndefined)
+                    throw Error(filename + " keeps a group's links in a fractal heap (more than 8 links with libver 'latest'), which this reader does not support");
+                break;
+            }
+            case 0x0006: {
+                // link message: version 1, flags (bits 0-1: width of the name length, 2: creation order, 3: link type,
+                // 4: character set), [type], [creation order], [charset], name length, name; hard link: object header address
+                obj.is_group = true;
+                const uint8_t lf = body[1];
+                size_t off = 2;
+                uint8_t link_type = 0;
+                if (lf & 0x08) link_type = body[off++];
+                if (lf & 0x04) off += 8;
+                if (lf & 0x10) off += 1;
+                const int w = 1 << (lf & 3);
+                uint64_t name_len = 0;
+                std::memcpy(&name_len, body + off, w);
+                off += w;
+                if (off + name_len + 8 > size) break;
+                const std::string name(reinterpret_cast<const char*>(body + off), name_len);
+                off += name_len;
+                if (link_type == 0) obj.links[name] = get<uint64_t>(body + off);  // soft / external links are skipped
+                break;
+            }
             default:
                 break;
         }
@@ -331,8 +394,7 @@ void File::parse_messages(const std::vector<uint8_t>& block, Object& obj, std::v
 Object File::parse_object(uint64_t header_address) const {
     uint8_t head[16];
     read_at(header_address, head, 16);
-    if (std::memcmp(head, "OHDR", 4) == 0)
-        throw Error(filename + " uses version-2 object headers (libver 'latest'), which this reader does not support");
+    if (std::memcmp(head, "OHDR", 4) == 0) return parse_object_v2(header_address);
     if (head[0] != 1) throw Error("bad object header in " + filename);
     const uint32_t size = get<uint32_t>(head + 8);
     Object obj;
@@ -340,6 +402,55 @@ Object File::parse_object(uint64_t header_address) const {
     for (size_t b = 0; b < blocks.size(); ++b) {
         const std::vector<uint8_t> block = bytes_at(blocks[b].first, blocks[b].second);
         parse_messages(block, obj, blocks);
+    }
+    return obj;
+}
+
+// Version-2 object header (libver "latest"): "OHDR", version 2, flags, [four 4-byte times if flags & 0x20], [max compact /
+// min dense attribute counts if flags & 0x10], size of chunk 0 in 1 << (flags & 3) bytes, then messages
+// {type u8, size u16, flags u8, [creation order u16 if flags & 0x04]} ... and a 4-byte checksum; continuation blocks are
+// "OCHK" + messages + checksum. Messages are not padded. The bodies are those of version-1 headers, plus the link message
+// that replaces symbol tables; they are repacked as version-1 records so that one message parser serves both.
+Object File::parse_object_v2(uint64_t header_address) const {
+    uint8_t head[6];
+    read_at(header_address, head, 6);
+    if (head[4] != 2) throw Error("bad version-2 object header in " + filename);
+    const uint8_t flags = head[5];
+    uint64_t p = header_address + 6;
+    if (flags & 0x20) p += 16;
+    if (flags & 0x10) p += 4;
+    const int size_bytes = 1 << (flags & 3);
+    uint8_t sz[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    read_at(p, sz, size_bytes);
+    const uint64_t chunk0 = get<uint64_t>(sz);
+    p += size_bytes;
+    const size_t prefix = (flags & 0x04) ? 6 : 4;
+    Object obj;
+    std::vector<std::pair<uint64_t, uint64_t>> blocks = {{p, chunk0}};
+    for (size_t b = 0; b < blocks.size(); ++b) {
+        const std::vector<uint8_t> block = bytes_at(blocks[b].first, blocks[b].second);
+        std::vector<uint8_t> v1;
+        size_t q = 0;
+        while (q + prefix <= block.size()) {
+            const uint8_t type = block[q];
+            const uint16_t size = get<uint16_t>(&block[q + 1]);
+            const uint8_t mflags = block[q + 3];
+            if (q + prefix + size > block.size()) break;
+            const uint8_t* body = &block[q + prefix];
+            if (type == 0x10) {
+                // continuation: the block starts with "OCHK" and ends with a checksum
+                blocks.emplace_back(get<uint64_t>(body) + 4, get<uint64_t>(body + 8) - 8);
+            } else if (type != 0) {
+                const uint16_t padded = (uint16_t)pad8(size);
+                const uint8_t rec[8] = {type, 0, (uint8_t)(padded & 0xff), (uint8_t)(padded >> 8), mflags, 0, 0, 0};
+                v1.insert(v1.end(), rec, rec + 8);
+                v1.insert(v1.end(), body, body + size);
+                v1.resize(v1.size() + (padded - size), 0);
+            }
+            q += prefix + size;
+        }
+        std::vector<std::pair<uint64_t, uint64_t>> none;
+        parse_messages(v1, obj, none);
     }
     return obj;
 }
@@ -405,6 +516,96 @@ void File::read_chunked(const Dataset& d, std::vector<uint8_t>& whole) const {
     uint64_t chunk_elems = 1;
     for (uint64_t c : d.chunk_dims) chunk_elems *= c;
 
+    // one chunk: read, undo the filters, scatter its rows into the row-major whole (last dimension contiguous)
+    auto place = [&](const std::vector<uint64_t>& off, uint64_t address, uint64_t stored, uint32_t mask) {
+        std::vector<uint8_t> chunk = bytes_at(address, stored);
+        for (size_t f = d.filters.size(); f-- > 0;) {  // undo the pipeline in reverse order
+            if (mask & (1u << f)) continue;
+            if (d.filters[f] == 1) {
+                std::vector<uint8_t> out(chunk_elems * elem);
+                uLongf out_len = out.size();
+                if (uncompress(out.data(), &out_len, chunk.data(), chunk.size()) != Z_OK)
+                    throw Error("cannot inflate a chunk of " + filename);
+                out.resize(out_len);
+                chunk.swap(out);
+            } else if (d.filters[f] == 2) {
+                unshuffle(chunk, elem);
+            } else {
+                throw Error("unsupported filter " + std::to_string(d.filters[f]) + " in " + filename);
+            }
+        }
+        if (chunk.size() < chunk_elems * elem) throw Error("short chunk in " + filename);
+        std::vector<uint64_t> idx(rank, 0);
+        const uint64_t last = d.chunk_dims[rank - 1];
+        const uint64_t rows = chunk_elems / last;
+        for (uint64_t r = 0; r < rows; ++r) {
+            uint64_t rem = r;
+            for (size_t k = rank - 1; k-- > 0;) {
+                idx[k] = rem % d.chunk_dims[k];
+                rem /= d.chunk_dims[k];
+            }
+            bool inside = true;
+            uint64_t flat = 0;
+            for (size_t k = 0; k + 1 < rank; ++k) {
+                const uint64_t g = off[k] + idx[k];
+                if (g >= d.dims[k]) inside = false;
+                flat = flat * d.dims[k] + g;
+            }
+            if (!inside || off[rank - 1] >= d.dims[rank - 1]) continue;
+            const uint64_t n = std::min<uint64_t>(last, d.dims[rank - 1] - off[rank - 1]);
+            std::memcpy(&whole[(flat * d.dims[rank - 1] + off[rank - 1]) * elem], &chunk[r * last * elem], n * elem);
+        }
+    };
+    if (d.address == kUndefined) return;  // nothing allocated: fill value
+
+    if (d.chunk_index != 0) {
+        // layout version 4. Chunks are numbered in row-major order of the chunk grid.
+        std::vector<uint64_t> grid(rank);
+        uint64_t nchunks = 1;
+        for (size_t k = 0; k < rank; ++k) {
+            grid[k] = (d.dims[k] + d.chunk_dims[k] - 1) / d.chunk_dims[k];
+            nchunks *= grid[k];
+        }
+        auto offsets_of = [&](uint64_t c) {
+            std::vector<uint64_t> off(rank);
+            for (size_t k = rank; k-- > 0;) {
+                off[k] = (c % grid[k]) * d.chunk_dims[k];
+                c /= grid[k];
+            }
+            return off;
+        };
+        const uint64_t plain = chunk_elems * elem;
+        if (d.chunk_index == 1) {  // one chunk holds the whole dataset
+            place(std::vector<uint64_t>(rank, 0), d.address, d.single_chunk_size ? d.single_chunk_size : plain,
+                  d.single_chunk_size ? d.single_filter_mask : 0);
+        } else if (d.chunk_index == 2) {  // implicit: every chunk allocated, one after the other, unfiltered
+            for (uint64_t c = 0; c < nchunks; ++c) place(offsets_of(c), d.address + c * plain, plain, 0);
+        } else {  // fixed array: header "FAHD" -> data block "FADB" -> one element per chunk
+            uint8_t h[28];
+            read_at(d.address, h, 28);
+            if (std::memcmp(h, "FAHD", 4) != 0) throw Error("bad fixed-array header in " + filename);
+            const int client = h[5], entry = h[6], page_bits = h[7];
+            const uint64_t nelem = get<uint64_t>(h + 8), block = get<uint64_t>(h + 16);
+            if (block == kUndefined) return;
+            if (nelem > (uint64_t(1) << page_bits))
+                throw Error(filename + ": paged fixed-array chunk index (more than " + std::to_string(1u << page_bits) + " chunks) is not supported by this reader");
+            const std::vector<uint8_t> elems = bytes_at(block + 14, (size_t)nelem * entry);  // "FADB", version, client, header address
+            for (uint64_t c = 0; c < std::min(nelem, nchunks); ++c) {
+                const uint8_t* e = &elems[(size_t)c * entry];
+                const uint64_t address = get<uint64_t>(e);
+                if (address == kUndefined) continue;
+                if (client == 0) {
+                    place(offsets_of(c), address, plain, 0);
+                } else {  // filtered chunks: address, stored size (entry - 12 bytes wide), filter mask
+                    uint64_t stored = 0;
+                    std::memcpy(&stored, e + 8, entry - 12);
+                    place(offsets_of(c), address, stored, get<uint32_t>(e + entry - 4));
+                }
+            }
+        }
+        return;
+    }
+
     // depth-first over the v1 chunk B-tree (node type 1); key = chunk size (4), filter mask (4), offsets (rank + 1) x 8
     std::vector<uint64_t> stack = {d.address};
     const size_t key_bytes = 8 + 8 * (rank + 1);
@@ -424,48 +625,9 @@ void File::read_chunked(const Dataset& d, std::vector<uint8_t>& whole) const {
                 stack.push_back(child);
                 continue;
             }
-            const uint32_t stored = get<uint32_t>(key);
-            const uint32_t mask = get<uint32_t>(key + 4);
             std::vector<uint64_t> off(rank);
             for (size_t r = 0; r < rank; ++r) off[r] = get<uint64_t>(key + 8 + 8 * r);
-            std::vector<uint8_t> chunk = bytes_at(child, stored);
-            for (size_t f = d.filters.size(); f-- > 0;) {  // undo the pipeline in reverse order
-                if (mask & (1u << f)) continue;
-                if (d.filters[f] == 1) {
-                    std::vector<uint8_t> out(chunk_elems * elem);
-                    uLongf out_len = out.size();
-                    if (uncompress(out.data(), &out_len, chunk.data(), chunk.size()) != Z_OK)
-                        throw Error("cannot inflate a chunk of " + filename);
-                    out.resize(out_len);
-                    chunk.swap(out);
-                } else if (d.filters[f] == 2) {
-                    unshuffle(chunk, elem);
-                } else {
-                    throw Error("unsupported filter " + std::to_string(d.filters[f]) + " in " + filename);
-                }
-            }
-            if (chunk.size() < chunk_elems * elem) throw Error("short chunk in " + filename);
-            // scatter the chunk's rows into the row-major whole (last dimension contiguous)
-            std::vector<uint64_t> idx(rank, 0);
-            const uint64_t last = d.chunk_dims[rank - 1];
-            const uint64_t rows = chunk_elems / last;
-            for (uint64_t r = 0; r < rows; ++r) {
-                uint64_t rem = r;
-                for (size_t k = rank - 1; k-- > 0;) {
-                    idx[k] = rem % d.chunk_dims[k];
-                    rem /= d.chunk_dims[k];
-                }
-                bool inside = true;
-                uint64_t flat = 0;
-                for (size_t k = 0; k + 1 < rank; ++k) {
-                    const uint64_t g = off[k] + idx[k];
-                    if (g >= d.dims[k]) inside = false;
-                    flat = flat * d.dims[k] + g;
-                }
-                if (!inside || off[rank - 1] >= d.dims[rank - 1]) continue;
-                const uint64_t n = std::min<uint64_t>(last, d.dims[rank - 1] - off[rank - 1]);
-                std::memcpy(&whole[(flat * d.dims[rank - 1] + off[rank - 1]) * elem], &chunk[r * last * elem], n * elem);
-            }
+            place(off, child, get<uint32_t>(key), get<uint32_t>(key + 4));
         }
     }
 }

@@ -53,6 +53,9 @@ struct Dataset {
     std::vector<uint8_t> compact;
     std::vector<uint64_t> chunk_dims;  // without the trailing element-size entry
     std::vector<int> filters;          // 1 deflate, 2 shuffle
+    int chunk_index = 0;               // 0: version-1 B-tree; layout version 4: 1 single chunk, 2 implicit, 3 fixed array
+    uint64_t single_chunk_size = 0;    // single filtered chunk: its stored size and filter mask
+    uint32_t single_filter_mask = 0;
     uint64_t elements() const {
         uint64_t n = 1;
         for (uint64_t d : dims) n *= d;
@@ -103,6 +106,7 @@ private:
     void read_at(uint64_t address, void* dst, size_t bytes) const;
     std::vector<uint8_t> bytes_at(uint64_t address, size_t bytes) const;
     Object parse_object(uint64_t header_address) const;
+    Object parse_object_v2(uint64_t header_address) const;
     void parse_messages(const std::vector<uint8_t>& block, Object& obj, std::vector<std::pair<uint64_t, uint64_t>>& more) const;
     void walk_group_btree(uint64_t btree, uint64_t heap_data, std::map<std::string, uint64_t>& links) const;
     void read_raw(const Dataset& d, uint64_t first_element, uint64_t count, std::vector<uint8_t>& out) const;

@@ -74,7 +74,7 @@ def test_rejects_what_it_cannot_read(tmp_path):
     p.write_bytes(b"definitely not hdf5" * 10)
     out = subprocess.run([os.path.join(HOST, "sart_b200_h5ls"), str(p)], capture_output=True, text=True)
     assert out.returncode == 1 and "is not an HDF5 file" in out.stderr
-    v2 = bytearray(bytes([0x89]) + b"HDF\r\n\x1a\n" + bytes([2]) + b"\0" * 100)
+    v2 = bytearray(bytes([0x89]) + b"HDF\r\n\x1a\n" + bytes([9]) + b"\0" * 100)  # a superblock version that does not exist
     p.write_bytes(bytes(v2))
     out = subprocess.run([os.path.join(HOST, "sart_b200_h5ls"), str(p)], capture_output=True, text=True)
     assert out.returncode == 1 and "not supported" in out.stderr
