@@ -7,8 +7,11 @@
 //   deflate and shuffle filters) layout, layout message versions 1-3, dataspace versions 1-2, attribute versions 1-3,
 //   datatypes: fixed-point (any width up to 8 bytes, signed or unsigned), IEEE float 4/8, fixed-length strings and
 //   variable-length strings (global heap). Little-endian data only. This is what h5py / libhdf5 1.8-1.14 write by default
-//   (libver "earliest"); files made with libver "latest" (version-2 object headers, fractal heaps) are rejected with a
-//   clear message.
+//   (libver "earliest"). Of the libver "latest" structures: superblock versions 2/3, version-2 object headers with
+//   continuation blocks, new-style groups whose links are link messages in the header (up to 8 links by default), layout
+//   message version 4 with contiguous, compact, single-chunk, implicit and unpaged fixed-array chunk storage (<= 1024
+//   chunks), filter pipeline version 2. Groups kept in a fractal heap, extensible-array and version-2 B-tree chunk indexes
+//   are refused with a clear message. (Checked against an independent pure-Python writer, tests/h5w.py.)
 // Writer: superblock 0, old-style groups (one symbol node per group, up to 64 links), contiguous datasets, version-1
 //   attribute messages, fixed-length strings, and EXTENDIBLE datasets: chunked layout (version-3 layout message, version-1
 //   chunk B-tree), first dimension unlimited, rows appended after the file has been laid out -- what the reference's

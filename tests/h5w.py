@@ -248,3 +248,95 @@ def write_chunked_h5(path, array, chunk, deflate=True, shuffle=True, vlen_attr=(
     blob[0:len(sb)] = sb
     with open(path, "wb") as f:
         f.write(bytes(blob))
+
+
+# ---- a "libver latest" style file, written from the format description -----------------------------------------------------
+
+def _msg2(mtype, body, flags=0):
+    """Version-2 object header message: type u8, size u16, flags u8, body (not padded)."""
+    return struct.pack("<BHB", mtype, len(body), flags) + body
+
+
+def _ohdr(messages, extra_block=None):
+    """"OHDR" header with one chunk; ``extra_block`` = (address, length) of a continuation block to point at."""
+    body = b"".join(messages)
+    if extra_block is not None:
+        body += _msg2(0x10, struct.pack("<QQ", *extra_block))
+    # flags 0x01: chunk-0 size in two bytes; checksum left zero (readers here do not verify it)
+    return b"OHDR" + bytes([2, 0x01]) + struct.pack("<H", len(body)) + body + b"\0\0\0\0"
+
+
+def write_latest_h5(path, a, attr_value=2.5):
+    """Superblock 2 -> root group (link messages) -> group "g" -> the float64 matrix ``a`` stored five ways under layout
+    version 4: contiguous, compact, a single chunk, implicit chunks, fixed-array-indexed deflated chunks. One dataset's
+    header continues in an "OCHK" block. For the reader features that no writer of this repository produces."""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    rows, cols = a.shape
+    UNDEF = 0xFFFFFFFFFFFFFFFF
+    blob = bytearray(b"\0" * 48)
+
+    def alloc(data):
+        while len(blob) % 8:
+            blob.append(0)
+        addr = len(blob)
+        blob.extend(data)
+        return addr
+
+    dtype_f64 = bytes([0x11, 0x20, 63, 0]) + struct.pack("<IHH4BI", 8, 0, 64, 52, 11, 0, 52, 1023)
+    space = struct.pack("<BBBB", 2, 2, 0, 1) + struct.pack("<QQ", rows, cols)  # dataspace version 2, simple
+    common = [_msg2(1, space), _msg2(3, dtype_f64, 1)]
+    links = {}
+
+    # contiguous
+    addr = alloc(a.tobytes())
+    links["contiguous"] = alloc(_ohdr(common + [_msg2(8, struct.pack("<BBQQ", 4, 1, addr, a.nbytes))]))
+    # compact (data inside the layout message)
+    small = a[:2, :3].copy()
+    sp_small = struct.pack("<BBBB", 2, 2, 0, 1) + struct.pack("<QQ", 2, 3)
+    links["compact"] = alloc(_ohdr([_msg2(1, sp_small), _msg2(3, dtype_f64, 1),
+                                    _msg2(8, struct.pack("<BBH", 4, 0, small.nbytes) + small.tobytes())]))
+    # a single chunk as large as the dataset; its header continues in a second block that holds an attribute
+    addr = alloc(a.tobytes())
+    lay = struct.pack("<BBBBB", 4, 2, 0, 3, 4) + struct.pack("<III", rows, cols, 8) + bytes([1]) + struct.pack("<Q", addr)
+    name = b"scale\0"
+    attr = struct.pack("<BBHHHB", 3, 0, len(name), len(dtype_f64), 4, 0) + name + dtype_f64 + struct.pack("<BBBB", 2, 0, 0, 0)
+    attr += struct.pack("<d", attr_value)
+    ochk = b"OCHK" + _msg2(0xC, attr) + b"\0\0\0\0"
+    ochk_addr = alloc(ochk)
+    links["single"] = alloc(_ohdr(common + [_msg2(8, lay)], extra_block=(ochk_addr, len(ochk))))
+    # implicit index: all chunks allocated in chunk-grid order from one address, no filters
+    cr, cc = max(1, rows // 3), max(1, cols // 2)
+    tiles = []
+    for r0 in range(0, rows, cr):
+        for c0 in range(0, cols, cc):
+            tile = np.zeros((cr, cc))
+            sub = a[r0:r0 + cr, c0:c0 + cc]
+            tile[:sub.shape[0], :sub.shape[1]] = sub
+            tiles.append(tile)
+    addr = alloc(b"".join(t.tobytes() for t in tiles))
+    lay = struct.pack("<BBBBB", 4, 2, 0, 3, 4) + struct.pack("<III", cr, cc, 8) + bytes([2]) + struct.pack("<Q", addr)
+    links["implicit"] = alloc(_ohdr(common + [_msg2(8, lay)]))
+    # fixed-array index over deflated chunks (client 1: address, stored size, filter mask per chunk)
+    elems = b""
+    for t in tiles:
+        raw = zlib.compress(t.tobytes(), 6)
+        elems += struct.pack("<QII", alloc(raw), len(raw), 0)
+    fahd_addr = alloc(b"\0" * 28)
+    fadb_addr = alloc(b"FADB" + bytes([0, 1]) + struct.pack("<Q", fahd_addr) + elems + b"\0\0\0\0")
+    blob[fahd_addr:fahd_addr + 28] = b"FAHD" + bytes([0, 1, 16, 10]) + struct.pack("<QQ", len(tiles), fadb_addr) + b"\0\0\0\0"
+    lay = struct.pack("<BBBBB", 4, 2, 0, 3, 4) + struct.pack("<III", cr, cc, 8) + bytes([3, 10]) + struct.pack("<Q", fahd_addr)
+    pipeline = struct.pack("<BB", 2, 1) + struct.pack("<HHH", 1, 0, 1) + struct.pack("<I", 6)
+    links["fixed_array"] = alloc(_ohdr(common + [_msg2(8, lay), _msg2(0xB, pipeline)]))
+
+    def link(name, target):  # hard link, one-byte name length, no optional fields
+        n = name.encode()
+        return _msg2(6, struct.pack("<BBB", 1, 0, len(n)) + n + struct.pack("<Q", target))
+
+    link_info = _msg2(2, struct.pack("<BBQQ", 0, 0, UNDEF, UNDEF))  # compact storage: no fractal heap
+    group = alloc(_ohdr([link_info] + [link(k, v) for k, v in sorted(links.items())]))
+    root = alloc(_ohdr([link_info, link("g", group)]))
+    sb = bytes([0x89]) + b"HDF\r\n\x1a\n" + bytes([2, 8, 8, 0]) + struct.pack("<QQQQ", 0, UNDEF, len(blob), root) + b"\0\0\0\0"
+    blob[0:len(sb)] = sb
+    with open(path, "wb") as f:
+        f.write(bytes(blob))
+    return small

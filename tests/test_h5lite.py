@@ -129,3 +129,22 @@ def test_extendible_datasets_grow_flush_by_flush(tmp_path):
         check()
     w.close()
     check()
+
+
+def test_reads_libver_latest_structures(tmp_path):
+    """Superblock 2, version-2 object headers (one with a continuation block), new-style groups with link messages, layout
+    version 4 with contiguous / compact / single-chunk / implicit / fixed-array storage: what h5py writes with
+    libver="latest" for small groups, here from an independent pure-Python writer (tests/h5w.py)."""
+    from tests.h5w import write_latest_h5
+    p = tmp_path / "latest.h5"
+    a = np.random.default_rng(4).standard_normal((7, 10))
+    small = write_latest_h5(p, a, attr_value=2.5)
+    o = h5ls(p)
+    assert o["g"]["kind"] == "group"
+    for name in ("contiguous", "single", "implicit", "fixed_array"):
+        d = o["g/" + name]
+        assert d["dims"] == [7, 10] and d["class"] == "float" and d["size"] == 8, (name, d)
+        np.testing.assert_array_equal(np.array(d["values"]).reshape(7, 10), a, err_msg=name)
+    np.testing.assert_array_equal(np.array(o["g/compact"]["values"]).reshape(2, 3), small)
+    assert o["g/single"]["attributes"] == {"scale": 2.5}
+    assert o["g/contiguous"]["layout"] == 1 and o["g/fixed_array"]["layout"] == 2
