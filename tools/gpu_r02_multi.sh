@@ -12,8 +12,10 @@ timeout 900 python -m pytest tests/test_multi_gpu.py -m gpu -v 2>&1 | tail -12 |
 echo "== bench N=$N =="
 timeout 900 $TR --master-port 29541 bench.py --gpus $N --extra-c3 on > gpurun_out/r02_bench_n$N.json 2> gpurun_out/r02_bench_n$N.err; echo "rc=$?"
 python tools/bench_brief.py < gpurun_out/r02_bench_n$N.json; tail -2 gpurun_out/r02_bench_n$N.err
-echo "== bench N=$N, run-ahead producer off =="
-SART_PREFETCH=0 timeout 600 $TR --master-port 29542 bench.py --gpus $N --no-check --extra-c3 off 2>/dev/null | tee gpurun_out/r02_bench_n${N}_noprefetch.json | python tools/bench_brief.py
+if [ "${3:-}" != "fast" ]; then
+  echo "== bench N=$N, run-ahead producer off =="
+  SART_PREFETCH=0 timeout 600 $TR --master-port 29542 bench.py --gpus $N --no-check --extra-c3 off 2>/dev/null | tee gpurun_out/r02_bench_n${N}_noprefetch.json | python tools/bench_brief.py
+fi
 echo "== c4 series N=$N ($FRAMES frames) =="
 timeout 1500 $TR --master-port 29543 bench.py --gpus $N --workload c4 --frames $FRAMES > gpurun_out/r02_c4_series_n$N.json 2> gpurun_out/r02_c4_series_n$N.err; echo "rc=$?"
 python tools/bench_brief.py < gpurun_out/r02_c4_series_n$N.json; tail -2 gpurun_out/r02_c4_series_n$N.err
