@@ -175,6 +175,7 @@ struct sart_engine {
     // several frames per matrix pass (sart_solve_batch): geometry + buffers for kGroup frames, allocated on first use
     bool group_planned = false, group_ok = false;
     uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
+    int group_frames = 8, gp_fp_rows = 4;  // frames per matrix pass and rows per thread of the batched forward kernel
     double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr;
     double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
     float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
@@ -1045,8 +1046,16 @@ int run_solve(sart_engine* e, int has_guess) {
 // every pass over it (fp_rows_batch_kernel / bp_cols_batch_kernel): 2 passes per iteration for the whole group instead of
 // one fused pass per frame. Linear solver; with several ranks the per-frame sums travel in one NCCL all-reduce per
 // pass. The log solver and a last single frame are solved frame by frame by the caller.
-constexpr int kGroup = 4;
-constexpr int kGroupFpRows = 8;
+// Group size: 8 frames per pass (forward kernel: 4 rows x 8 frames of accumulators per thread) or 4 (8 rows x 4 frames);
+// SART_BATCH_FRAMES picks, buffers are sized for kGroup = the larger one.
+constexpr int kGroup = 8;
+
+template <int F>
+struct GroupKernels {
+    static constexpr int kFpRows = 32 / F;  // rows x frames = 32 accumulators per thread either way
+    static void (*fp())(const FpBatchArgs) { return fp_rows_batch_kernel<kFpRows, kFpThreads, F>; }
+    static void (*bp())(const BpBatchArgs) { return bp_cols_batch_kernel<kBpThreads, 8, F>; }
+};
 
 int plan_group(sart_engine* e) {
     if (e->group_planned) return SART_OK;
@@ -1054,9 +1063,16 @@ int plan_group(sart_engine* e) {
     e->group_ok = false;
     if (e->cfg.logarithmic) return SART_OK;
     int fp_occ = 0, bp_occ = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, fp_rows_batch_kernel<kGroupFpRows, kFpThreads, kGroup>, kFpThreads, 0));
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, bp_cols_batch_kernel<kBpThreads, 8, kGroup>, kBpThreads, 0));
-    const uint64_t nrg = ceil_div(e->P, kGroupFpRows);
+    e->group_frames = env_int("SART_BATCH_FRAMES", 8) >= 8 ? 8 : 4;
+    e->gp_fp_rows = 32 / e->group_frames;
+    if (e->group_frames == 8) {
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, GroupKernels<8>::fp(), kFpThreads, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, GroupKernels<8>::bp(), kBpThreads, 0));
+    } else {
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, GroupKernels<4>::fp(), kFpThreads, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, GroupKernels<4>::bp(), kBpThreads, 0));
+    }
+    const uint64_t nrg = ceil_div(e->P, (uint64_t)e->gp_fp_rows);
     e->gp_fp_grid = (uint32_t)std::min<uint64_t>(nrg, (uint64_t)e->sm_count * std::max(fp_occ, 1));
     // back projection: one wave of (panels x slabs) CTAs at this kernel's own occupancy, slabs a multiple of 32 rows
     const uint64_t panels = ceil_div(e->ld4, kBpThreads);
@@ -1102,7 +1118,7 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         b.rows_per_slab = e->gp_bp_rows_per_slab;
         b.st = st;
         b.nframes = nf;
-        bp_cols_batch_kernel<kBpThreads, 8, kGroup>
+        (e->group_frames == 8 ? GroupKernels<8>::bp() : GroupKernels<4>::bp())
             <<<dim3((uint32_t)ceil_div(e->ld4, kBpThreads), e->gp_bp_slabs), kBpThreads, 0, e->stream>>>(b);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
@@ -1151,10 +1167,10 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         a.w = e->d_pw;
         a.f2part = e->d_pf2part;
         a.st = st_in;
-        a.nrg = (uint32_t)ceil_div(P, kGroupFpRows);
+        a.nrg = (uint32_t)ceil_div(P, (uint64_t)e->gp_fp_rows);
         a.nframes = nf;
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
-        fp_rows_batch_kernel<kGroupFpRows, kFpThreads, kGroup><<<e->gp_fp_grid, kFpThreads, 0, e->stream>>>(a);
+        (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, kFpThreads, 0, e->stream>>>(a);
         CUDA_TRY(cudaGetLastError());
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;
@@ -2064,7 +2080,7 @@ int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements
     double total_ms = 0;
     uint64_t h2d = 0, d2h = 0;
     while (f < nframes) {
-        const int nf = std::min<int32_t>(kGroup, nframes - f);
+        const int nf = std::min<int32_t>(e->group_frames, nframes - f);
         if (e->group_ok && nf >= 2) {
             e->launches = 0;
             CUDA_TRY(cudaEventRecord(e->ev_solve0, e->stream));
