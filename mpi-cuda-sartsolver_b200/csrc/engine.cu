@@ -175,7 +175,7 @@ struct sart_engine {
     // several frames per matrix pass (sart_solve_batch): geometry + buffers for kGroup frames, allocated on first use
     bool group_planned = false, group_ok = false;
     uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
-    int group_frames = 8, gp_fp_rows = 4;  // frames per matrix pass and rows per thread of the batched forward kernel
+    int group_frames = 8, gp_fp_rows = 8, gp_fp_threads = 384;  // frames per matrix pass; rows per thread / threads per CTA of the batched forward kernel
     double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr;
     double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
     float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
@@ -1050,11 +1050,21 @@ int run_solve(sart_engine* e, int has_guess) {
 // SART_BATCH_FRAMES picks, buffers are sized for kGroup = the larger one.
 constexpr int kGroup = 8;
 
+constexpr int kFp8Threads = 384, kFp8Rows = 8;  // eight frames: 8 rows x 8 frames of accumulators per thread, one CTA per SM
 template <int F>
 struct GroupKernels {
-    static constexpr int kFpRows = 32 / F;  // rows x frames = 32 accumulators per thread either way
-    static void (*fp())(const FpBatchArgs) { return fp_rows_batch_kernel<kFpRows, kFpThreads, F>; }
-    static void (*bp())(const BpBatchArgs) { return bp_cols_batch_kernel<kBpThreads, 8, F>; }
+    static constexpr int kFpRows = (F >= 8) ? kFp8Rows : 32 / F;
+    static constexpr int kFpThreadsOf = (F >= 8) ? kFp8Threads : kFpThreads;
+    // eight frames: a row group per warp (x shared through L1) and weights from shared memory; four: a row group per CTA
+    // and weights by shuffle (kernels.cuh)
+    static void (*fp())(const FpBatchArgs) {
+        if (F >= 8) return fp_rows_batch_warp_kernel<kFp8Rows, kFp8Threads, F, 1>;
+        return fp_rows_batch_kernel<32 / F, kFpThreads, F>;
+    }
+    static void (*bp())(const BpBatchArgs) {
+        if (F >= 8) return bp_cols_batch_smem_kernel<kBpThreads, 8, F>;
+        return bp_cols_batch_kernel<kBpThreads, 8, F>;
+    }
 };
 
 int plan_group(sart_engine* e) {
@@ -1064,16 +1074,18 @@ int plan_group(sart_engine* e) {
     if (e->cfg.logarithmic) return SART_OK;
     int fp_occ = 0, bp_occ = 0;
     e->group_frames = env_int("SART_BATCH_FRAMES", 8) >= 8 ? 8 : 4;
-    e->gp_fp_rows = 32 / e->group_frames;
+    e->gp_fp_rows = e->group_frames == 8 ? GroupKernels<8>::kFpRows : GroupKernels<4>::kFpRows;
+    e->gp_fp_threads = e->group_frames == 8 ? GroupKernels<8>::kFpThreadsOf : GroupKernels<4>::kFpThreadsOf;
     if (e->group_frames == 8) {
-        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, GroupKernels<8>::fp(), kFpThreads, 0));
+        CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, GroupKernels<8>::fp(), kFp8Threads, 0));
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, GroupKernels<8>::bp(), kBpThreads, 0));
     } else {
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fp_occ, GroupKernels<4>::fp(), kFpThreads, 0));
         CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bp_occ, GroupKernels<4>::bp(), kBpThreads, 0));
     }
     const uint64_t nrg = ceil_div(e->P, (uint64_t)e->gp_fp_rows);
-    e->gp_fp_grid = (uint32_t)std::min<uint64_t>(nrg, (uint64_t)e->sm_count * std::max(fp_occ, 1));
+    const uint64_t groups_per_cta = e->group_frames == 8 ? kFp8Threads / 32 : 1;
+    e->gp_fp_grid = (uint32_t)std::min<uint64_t>(ceil_div(nrg, groups_per_cta), (uint64_t)e->sm_count * std::max(fp_occ, 1));
     // back projection: one wave of (panels x slabs) CTAs at this kernel's own occupancy, slabs a multiple of 32 rows
     const uint64_t panels = ceil_div(e->ld4, kBpThreads);
     uint64_t slabs = std::max<uint64_t>(1, (uint64_t)e->sm_count * std::max(bp_occ, 1) / panels);
@@ -1170,7 +1182,7 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         a.nrg = (uint32_t)ceil_div(P, (uint64_t)e->gp_fp_rows);
         a.nframes = nf;
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
-        (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, kFpThreads, 0, e->stream>>>(a);
+        (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, e->gp_fp_threads, 0, e->stream>>>(a);
         CUDA_TRY(cudaGetLastError());
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;

@@ -379,6 +379,94 @@ __global__ void __launch_bounds__(NT, 2) fp_rows_batch_kernel(const FpBatchArgs 
     }
 }
 
+// The same for wide groups (F = 8), where re-reading x dominates: above, a CTA walks ONE row group and every thread
+// fetches F float4 of x per column step -- with F = 8 that is twice the bytes of the matrix itself coming out of L2.
+// Here every WARP owns a row group of R rows (R * F = 32 accumulators per thread, lane l reads columns l, l + 32, ...)
+// and the warps of a CTA walk the columns side by side, so a column step's x values are fetched from L2 once per CTA
+// and found in L1 by the other warps. A row's dot products never leave the warp: shuffle tree, lane r * F + f finishes
+// (row r, frame f).
+template <int R, int NT, int F, int MINB>
+__global__ void __launch_bounds__(NT, MINB) fp_rows_batch_warp_kernel(const FpBatchArgs a) {
+    static_assert((R * F) % 32 == 0 && 32 % F == 0, "whole (row, frame) slots per lane in the epilogue");
+    constexpr int PER_LANE = R * F / 32;  // lane l finishes (row l / F + q * 32 / F, frame l % F), q < PER_LANE
+    if (a.st) {
+        bool all_done = true;
+        for (int f = 0; f < a.nframes; ++f) all_done = all_done && a.st[f].done;
+        if (all_done) return;
+    }
+    constexpr int NW = NT / 32;
+    __shared__ double f2s[NW][F];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float4* __restrict__ H4 = reinterpret_cast<const float4*>(a.H);
+    const float4* __restrict__ x4 = reinterpret_cast<const float4*>(a.x);
+    const uint32_t ld4 = (uint32_t)a.ld4;
+    const int my_r = lane / F, my_f = lane % F;
+    double f2acc = 0.0;  // of frame my_f, this lane's row slots
+
+    for (uint32_t rg = blockIdx.x * NW + warp; rg < a.nrg; rg += gridDim.x * NW) {
+        const uint64_t row0 = (uint64_t)rg * R;
+        const int nvalid = (int)min((uint64_t)R, a.P - row0);
+        const float4* __restrict__ base = H4 + row0 * a.ld4;
+        uint32_t roff[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) roff[r] = (r < nvalid ? r : 0) * ld4;
+        float acc[R][F];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int f = 0; f < F; ++f) acc[r][f] = 0.f;
+#pragma unroll 1
+        for (uint32_t c = lane; c < ld4; c += 32) {
+            float4 xv[F], h[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) h[r] = ldg_stream(base + roff[r] + c);
+#pragma unroll
+            for (int f = 0; f < F; ++f) xv[f] = __ldg(x4 + (uint64_t)f * ld4 + c);
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+#pragma unroll
+                for (int f = 0; f < F; ++f) {
+                    acc[r][f] = fmaf(h[r].x, xv[f].x, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].y, xv[f].y, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].z, xv[f].z, acc[r][f]);
+                    acc[r][f] = fmaf(h[r].w, xv[f].w, acc[r][f]);
+                }
+        }
+        double mine[PER_LANE];
+#pragma unroll
+        for (int q = 0; q < PER_LANE; ++q) mine[q] = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+#pragma unroll
+            for (int f = 0; f < F; ++f) {
+                const double s = warp_sum((double)acc[r][f]);
+                if (lane == (r * F + f) % 32) mine[(r * F + f) / 32] = s;
+            }
+#pragma unroll
+        for (int q = 0; q < PER_LANE; ++q) {
+            const int r = my_r + q * (32 / F);
+            if (r < nvalid && my_f < a.nframes) {
+                const uint64_t i = row0 + r;
+                const float fitv = (float)mine[q];
+                f2acc += mine[q] * mine[q];
+                const float gi = a.g[(uint64_t)my_f * a.P + i];
+                a.w[(uint64_t)my_f * a.P + i] = (gi >= 0.f) ? (gi - fitv) * a.rinv[i] : 0.f;
+            }
+        }
+    }
+    // sum(fit^2) per frame: over the row slots of a warp (lanes f, f + F, ...), then over the warps in order
+#pragma unroll
+    for (int o = F; o < 32; o <<= 1) f2acc += __shfl_xor_sync(FULL_MASK, f2acc, o);
+    if (lane < F) f2s[warp][lane] = f2acc;
+    __syncthreads();
+    if ((int)threadIdx.x < a.nframes) {
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) s += f2s[k][threadIdx.x];
+        a.f2part[(uint64_t)threadIdx.x * gridDim.x + blockIdx.x] = s;
+    }
+}
+
 struct BpBatchArgs {
     const float* H;
     uint64_t ld4, P;
@@ -435,6 +523,75 @@ __global__ void __launch_bounds__(NT) bp_cols_batch_kernel(const BpBatchArgs a) 
             const int n = (int)(r1 - r);
             for (int k = 0; k < n; ++k) fma_row(ldg_stream(p + (uint64_t)k * a.ld4), wl, k);
         }
+    }
+    if (active) {
+        const uint64_t nslabs = gridDim.y;
+#pragma unroll
+        for (int f = 0; f < F; ++f)
+            if (f < a.nframes) reinterpret_cast<float4*>(a.part)[((uint64_t)f * nslabs + blockIdx.y) * a.ld4 + c4] = acc[f];
+    }
+}
+
+// Wide groups (F = 8): the F weights of a row come out of shared memory (two broadcast 128-bit loads) instead of F
+// shuffles per row and thread; the weights of the next 32 rows are fetched while the current 32 are multiplied.
+template <int NT, int U, int F>
+__global__ void __launch_bounds__(NT) bp_cols_batch_smem_kernel(const BpBatchArgs a) {
+    static_assert(NT >= 32 * F && F % 4 == 0, "one thread per (row, frame) of a 32-row block");
+    if (a.st) {
+        bool all_done = true;
+        for (int f = 0; f < a.nframes; ++f) all_done = all_done && a.st[f].done;
+        if (all_done) return;
+    }
+    __shared__ __align__(16) float ws[2][32][F];
+    const int tid = threadIdx.x;
+    const uint64_t c4 = (uint64_t)blockIdx.x * NT + tid;
+    const bool active = c4 < a.ld4;
+    const float4* __restrict__ base = reinterpret_cast<const float4*>(a.H) + (active ? c4 : a.ld4 - 1);
+    const uint64_t r0 = (uint64_t)blockIdx.y * a.rows_per_slab;
+    const uint64_t r1 = min(a.P, r0 + a.rows_per_slab);
+    const int wrow = tid & 31, wf = tid >> 5;  // this thread's (row, frame) of a block's weights
+    auto stage = [&](uint64_t r, int buf) {
+        if (wf < F) ws[buf][wrow][wf] = (r + wrow < r1 && wf < a.nframes) ? __ldg(a.w + (uint64_t)wf * a.P + r + wrow) : 0.f;
+    };
+    float4 acc[F];
+#pragma unroll
+    for (int f = 0; f < F; ++f) acc[f] = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto fma_row = [&](const float4& h, const float* wrow_ptr) {
+#pragma unroll
+        for (int f4 = 0; f4 < F / 4; ++f4) {
+            const float4 wv = *reinterpret_cast<const float4*>(wrow_ptr + 4 * f4);
+            const float wf4[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float4& ac = acc[4 * f4 + j];
+                ac.x = fmaf(h.x, wf4[j], ac.x);
+                ac.y = fmaf(h.y, wf4[j], ac.y);
+                ac.z = fmaf(h.z, wf4[j], ac.z);
+                ac.w = fmaf(h.w, wf4[j], ac.w);
+            }
+        }
+    };
+    int buf = 0;
+    if (r0 < r1) stage(r0, 0);
+    __syncthreads();
+    for (uint64_t r = r0; r < r1; r += 32) {
+        if (r + 32 < r1) stage(r + 32, buf ^ 1);
+        const float4* __restrict__ p = base + r * a.ld4;
+        if (r + 32 <= r1) {
+#pragma unroll
+            for (int k = 0; k < 32; k += U) {
+                float4 h[U];  // U unconditional 128-bit loads in flight before the first FMA
+#pragma unroll
+                for (int u = 0; u < U; ++u) h[u] = ldg_stream(p + (uint64_t)(k + u) * a.ld4);
+#pragma unroll
+                for (int u = 0; u < U; ++u) fma_row(h[u], &ws[buf][k + u][0]);
+            }
+        } else {
+            const int n = (int)(r1 - r);
+            for (int k = 0; k < n; ++k) fma_row(ldg_stream(p + (uint64_t)k * a.ld4), &ws[buf][k][0]);
+        }
+        __syncthreads();  // everybody is done with ws[buf]; ws[buf ^ 1] is complete
+        buf ^= 1;
     }
     if (active) {
         const uint64_t nslabs = gridDim.y;

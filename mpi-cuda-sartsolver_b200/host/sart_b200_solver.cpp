@@ -241,7 +241,7 @@ int main(int argc, char* argv[]) {
     std::vector<int32_t> all_status, all_iterations;
 
     // source/main.cpp:127-140. With --no_guess consecutive frames do not depend on each other, so they are handed to the
-    // engine four at a time (sart_solve_batch: every pass over the matrix serves the whole group).
+    // engine eight at a time (sart_solve_batch: every pass over the matrix serves the whole group).
     auto store = [&](size_t k, const double* x, int32_t status, int32_t iterations) {
         const double t = frames->frame_time(k);
         if (rank != 0) return;  // source/main.cpp:134: only the root stores solutions
@@ -281,7 +281,7 @@ int main(int argc, char* argv[]) {
     std::vector<double> solution_vec, frame;
     size_t k = 0;
     while (k < frames->size()) {
-        const size_t nb = config.no_guess ? std::min<size_t>(4, frames->size() - k) : 1;
+        const size_t nb = config.no_guess ? std::min<size_t>(8, frames->size() - k) : 1;
         if (nb >= 2) {
             std::vector<double> group_frames, group_solutions(nb * nvoxel);
             if (!frames->read_chunk(k, nb, offset_pixel, npixel_local, group_frames, error)) die(error);
