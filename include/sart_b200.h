@@ -219,7 +219,7 @@ int sart_solve_series(sart_engine* e, int32_t nframes, const double* measurement
  * with solution_vec.clear() after every frame -- in one call. Such frames are independent right-hand sides of the same
  * matrix, so the engine solves them eight at a time (SART_BATCH_FRAMES=4: four): every pass over the matrix (forward
  * projection, back projection) serves the whole group, 2 passes per iteration for eight frames instead of one fused pass per frame (linear solver,
- * any number of ranks; the log solver and a last single frame are solved one after the other, same results). COLLECTIVE.
+ * log solver, any number of ranks; a last single frame is solved on its own, same results). COLLECTIVE.
  *   measurements [nframes][nrows], solutions [nframes][nvoxel] (host, double); status, iterations [nframes] or NULL.
  * Every frame gets exactly what sart_solve(has_guess = 0) would give it, within the parity tolerance. */
 int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements, double* solutions, int32_t* status,

@@ -176,7 +176,7 @@ struct sart_engine {
     bool group_planned = false, group_ok = false;
     uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
     int group_frames = 8, gp_fp_rows = 8, gp_fp_threads = 384;  // frames per matrix pass; rows per thread / threads per CTA of the batched forward kernel
-    double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr;
+    double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr, *d_pobs = nullptr;
     double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
     float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
     float *d_pg = nullptr, *d_pw = nullptr, *d_ppart = nullptr;
@@ -1045,7 +1045,8 @@ int run_solve(sart_engine* e, int has_guess) {
 // Frames solved without a warm start are independent right-hand sides of the same matrix, so kGroup of them ride on
 // every pass over it (fp_rows_batch_kernel / bp_cols_batch_kernel): 2 passes per iteration for the whole group instead of
 // one fused pass per frame. Linear solver; with several ranks the per-frame sums travel in one NCCL all-reduce per
-// pass. The log solver and a last single frame are solved frame by frame by the caller.
+// pass. The log solver rides along (its back-projected measurement of every frame comes from one more batched pass at
+// set-up). A last single frame is solved on its own by the caller.
 // Group size: 8 frames per pass (forward kernel: 4 rows x 8 frames of accumulators per thread) or 4 (8 rows x 4 frames);
 // SART_BATCH_FRAMES picks, buffers are sized for kGroup = the larger one.
 constexpr int kGroup = 8;
@@ -1071,7 +1072,6 @@ int plan_group(sart_engine* e) {
     if (e->group_planned) return SART_OK;
     e->group_planned = true;
     e->group_ok = false;
-    if (e->cfg.logarithmic) return SART_OK;
     int fp_occ = 0, bp_occ = 0;
     e->group_frames = env_int("SART_BATCH_FRAMES", 8) >= 8 ? 8 : 4;
     e->gp_fp_rows = e->group_frames == 8 ? GroupKernels<8>::kFpRows : GroupKernels<4>::kFpRows;
@@ -1098,6 +1098,7 @@ int plan_group(sart_engine* e) {
     SART_TRY(dev_alloc(&e->d_pg, G * e->P));
     SART_TRY(dev_alloc(&e->d_pw, G * e->P));
     SART_TRY(dev_alloc(&e->d_pxio, G * e->V));
+    SART_TRY(dev_alloc(&e->d_pobs, G * e->V));
     SART_TRY(dev_alloc(&e->d_psred, G * (e->V + 2)));
     SART_TRY(dev_alloc(&e->d_pf2part, G * (uint64_t)e->gp_fp_grid));
     SART_TRY(dev_alloc(&e->d_pf2sum, G));
@@ -1145,18 +1146,34 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
 
     // per frame: statistics, normalisation, weights of the default initial guess; one pass back-projects all of them
     SART_TRY(compute_frame_stats(e, e->d_pgd, P, nf));  // all frames of the group together
-    for (int f = 0; f < nf; ++f) {
-        frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_stat_max + f, e->d_stat_sum + f,
-                                                             e->d_lambda, e->cfg.ray_length_threshold, e->d_pg + f * P, e->d_rinv,
-                                                             e->d_pw + f * P, gpu_sem ? 2 : 1);
-        CUDA_TRY(cudaGetLastError());
-        ++e->launches;
+    const bool log_mode = e->cfg.logarithmic != 0;
+    auto prepare = [&](int weights_mode) -> int {
+        for (int f = 0; f < nf; ++f) {
+            frame_prepare_kernel<<<pblocks, 256, 0, e->stream>>>(e->d_pgd + f * P, P, e->d_pfs + f, e->d_stat_max + f,
+                                                                 e->d_stat_sum + f, e->d_lambda, e->cfg.ray_length_threshold,
+                                                                 e->d_pg + f * P, e->d_rinv, e->d_pw + f * P, weights_mode);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+        }
+        return SART_OK;
+    };
+    if (log_mode) {  // the log solver's iteration-invariant back-projected measurement of every frame, in one pass
+        SART_TRY(prepare(3));
+        SART_TRY(back_project(nullptr));
+        for (int f = 0; f < nf; ++f) {
+            mask_obs_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_psred + f * (V + 2), e->d_rho, e->cfg.ray_density_threshold,
+                                                            e->d_pobs + f * V, V);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+        }
     }
+    SART_TRY(prepare(gpu_sem ? 2 : 1));
     SART_TRY(back_project(nullptr));
     for (int f = 0; f < nf; ++f) {
+        // lower clamp of the starting solution as in frame_prologue: GPU semantics 1e-7 (normalised), CPU log solver 1e-100
         start_solution_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_psred + f * (V + 2), nullptr, e->d_rho,
                                                               e->cfg.ray_density_threshold, e->d_pfs + f, gpu_sem ? 1.e-7 : 0.0,
-                                                              0.0, 0, e->d_pxd[0] + f * V, e->d_pxf[0] + f * ld, V);
+                                                              (!gpu_sem && log_mode) ? 1.e-100 : 0.0, 0, e->d_pxd[0] + f * V, e->d_pxf[0] + f * ld, V);
         init_state_kernel<<<1, 1, 0, e->stream>>>(e->d_pst[0] + f, e->d_pst[1] + f);
         CUDA_TRY(cudaGetLastError());
         e->launches += 2;
@@ -1181,6 +1198,7 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         a.st = st_in;
         a.nrg = (uint32_t)ceil_div(P, (uint64_t)e->gp_fp_rows);
         a.nframes = nf;
+        a.log_mode = e->cfg.logarithmic;
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
         (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, e->gp_fp_threads, 0, e->stream>>>(a);
         CUDA_TRY(cudaGetLastError());
@@ -1209,6 +1227,7 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
             u.xd_next = e->d_pxd[(t + 1) & 1] + f * V;
             u.xf_next = e->d_pxf[(t + 1) & 1] + f * ld;
             u.fs = e->d_pfs + f;
+            u.obs = e->d_pobs + f * V;
             update_kernel<<<vblocks, 256, 0, e->stream>>>(u);
             CUDA_TRY(cudaGetLastError());
             ++e->launches;
@@ -1468,7 +1487,7 @@ void free_engine(sart_engine* e) {
                            e->d_stat_part, e->d_stat_max, e->d_stat_sum};
     for (void* p : series_ptrs)
         if (p) cudaFree(p);
-    void* pair_ptrs[] = {e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
+    void* pair_ptrs[] = {e->d_pobs, e->d_pgd, e->d_pxio, e->d_psred, e->d_pf2part, e->d_pf2sum, e->d_pxd[0], e->d_pxd[1], e->d_pxf[0], e->d_pxf[1],
                          e->d_pg, e->d_pw, e->d_ppart, e->d_pfs, e->d_pst[0], e->d_pst[1]};
     for (void* p : pair_ptrs)
         if (p) cudaFree(p);

@@ -298,6 +298,7 @@ struct FpBatchArgs {
     const IterState* st;  // [F] or null
     uint32_t nrg;
     int nframes;          // frames in use (<= F); the others are skipped in the epilogue
+    int log_mode;         // log solver: w = fit / lambda instead of (g - fit) / lambda
 };
 
 template <int R, int NT, int F>
@@ -364,7 +365,7 @@ __global__ void __launch_bounds__(NT, 2) fp_rows_batch_kernel(const FpBatchArgs 
                 const float fitv = (float)s;
                 f2acc += s * s;
                 const float gi = a.g[(uint64_t)f * a.P + i];
-                a.w[(uint64_t)f * a.P + i] = (gi >= 0.f) ? (gi - fitv) * a.rinv[i] : 0.f;
+                a.w[(uint64_t)f * a.P + i] = (gi >= 0.f) ? (a.log_mode ? fitv : gi - fitv) * a.rinv[i] : 0.f;
             }
         }
         __syncthreads();
@@ -450,7 +451,7 @@ __global__ void __launch_bounds__(NT, MINB) fp_rows_batch_warp_kernel(const FpBa
                 const float fitv = (float)mine[q];
                 f2acc += mine[q] * mine[q];
                 const float gi = a.g[(uint64_t)my_f * a.P + i];
-                a.w[(uint64_t)my_f * a.P + i] = (gi >= 0.f) ? (gi - fitv) * a.rinv[i] : 0.f;
+                a.w[(uint64_t)my_f * a.P + i] = (gi >= 0.f) ? (a.log_mode ? fitv : gi - fitv) * a.rinv[i] : 0.f;
             }
         }
     }

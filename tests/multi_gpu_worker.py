@@ -66,16 +66,14 @@ def main():
         # warm-started second frame
         x2, st2, it2 = eng.solve(1.1 * g[off:off + n], x)
         x2_ref, st2_ref, it2_ref = res.solve(H, 1.1 * g, x0=x_ref, lap=lap, beta_laplace=2e-2, nranks=cp.world, **okw)
-        # independent frames through sart_solve_batch (four per matrix pass, per-frame sums all-reduced together)
-        batch = None
-        if not kw.get("logarithmic"):
-            frames = np.stack([(1.0 + 0.5 * k) * g[off:off + n] for k in range(5)])
-            xb, stb, itb = eng.solve_batch(frames)
-            singles = [eng.solve(f) for f in frames]
-            batch = {"x": max(rel_l2(xb[k], singles[k][0]) for k in range(5)),
-                     "same_status": bool(all(int(stb[k]) == singles[k][1] for k in range(5))),
-                     "iteration_gap": int(max(abs(int(itb[k]) - singles[k][2]) for k in range(5))),
-                     "hash": float(np.sum(xb[4] * np.arange(1, V + 1)))}
+        # independent frames through sart_solve_batch (one matrix pass serves all, per-frame sums all-reduced together)
+        frames = np.stack([(1.0 + 0.5 * k) * g[off:off + n] for k in range(5)])
+        xb, stb, itb = eng.solve_batch(frames)
+        singles = [eng.solve(f) for f in frames]
+        batch = {"x": max(rel_l2(xb[k], singles[k][0]) for k in range(5)),
+                 "same_status": bool(all(int(stb[k]) == singles[k][1] for k in range(5))),
+                 "iteration_gap": int(max(abs(int(itb[k]) - singles[k][2]) for k in range(5))),
+                 "hash": float(np.sum(xb[4] * np.arange(1, V + 1)))}
         # warm-started series through sart_solve_series (look-ahead) against solve-by-solve on the same ranks
         series = None
         if not kw.get("logarithmic"):

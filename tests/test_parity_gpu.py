@@ -557,19 +557,22 @@ def test_randomised_problems_against_the_oracle(seed, sart, restatement):
         np.testing.assert_array_equal(np.isfinite(x), np.isfinite(x_ref))
 
 
-@pytest.mark.parametrize("P,V,tol", [(700, 1000, None), (512, 50000, None), (300, 20000, 1e-4), (257, 77, 1e-4)])
-def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, sart, restatement):
-    """sart_solve_batch (four frames per matrix pass) against solving every frame on its own and against the oracle: seven
+@pytest.mark.parametrize("P,V,tol,log", [(700, 1000, None, False), (512, 50000, None, False), (300, 20000, 1e-4, False),
+                                          (257, 77, 1e-4, False), (700, 1000, None, True), (300, 5000, 1e-4, True)])
+def test_batch_of_independent_frames_matches_frame_by_frame(P, V, tol, log, sart, restatement):
+    """sart_solve_batch (eight frames per matrix pass) against solving every frame on its own and against the oracle: eleven
     frames, so one full group and one of three; frames of a group converge at different iterations when the tolerance
-    decides."""
+    decides. Both solvers: the log solver's back-projected measurement of every frame is one more batched pass."""
     syn = load_synthetic()
     H = restatement.fill_synthetic(P, V, 321)
-    times = (0.0, 0.3, 0.55, 0.8, 1.0, 0.15, 0.65)
+    times = (0.0, 0.3, 0.55, 0.8, 1.0, 0.15, 0.65, 0.9, 0.45, 0.05, 0.7)
     frames = np.stack([restatement.forward(H, syn.emission_profile(V, t=t) * (1.0 + 3.0 * t)) for t in times])
     frames[1, ::19] = -1.0
     lap = syn.laplacian_coo(V)
     kw = dict(beta_laplace=2e-2, max_iterations=9, fixed_iterations=True) if tol is None else \
         dict(beta_laplace=2e-2, max_iterations=300, conv_tolerance=tol)
+    if log:
+        kw.update(logarithmic=True, relaxation=0.8)
     with sart.Engine(P, V, device=0, **kw) as eng:
         eng.upload_rows(H)
         eng.set_laplacian(*lap)
