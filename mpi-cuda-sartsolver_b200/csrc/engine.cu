@@ -1121,7 +1121,9 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
     const uint64_t P = e->P, V = e->V, ld = e->ld;
     const uint64_t part_stride = (uint64_t)e->gp_bp_slabs * ld;
 
-    auto back_project = [&](const IterState* st) -> int {  // d_pw -> d_psred[f], every frame in one pass
+    const bool multi = e->cfg.nranks > 1;
+    const dim3 vgrid(vblocks, (uint32_t)nf);  // one CTA row per frame: the per-frame steps of all frames in one launch
+    auto launch_bp = [&](const IterState* st) -> int {  // d_pw -> slab partials, every frame in one pass
         BpBatchArgs b;
         b.H = e->dH;
         b.ld4 = e->ld4;
@@ -1135,13 +1137,20 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
             <<<dim3((uint32_t)ceil_div(e->ld4, kBpThreads), e->gp_bp_slabs), kBpThreads, 0, e->stream>>>(b);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
-        for (int f = 0; f < nf; ++f) {
-            reduce_partials_kernel<<<vblocks, 256, 0, e->stream>>>(e->d_ppart + f * part_stride, e->gp_bp_slabs, ld, V,
-                                                                   e->d_psred + f * (V + 2), st ? st + f : nullptr);
-            CUDA_TRY(cudaGetLastError());
-            ++e->launches;
-        }
-        return allreduce_f64(e, e->d_psred, (uint64_t)nf * (V + 2), ncclSum);  // over the row shards, all frames at once
+        return SART_OK;
+    };
+    // slab partials -> dst[f * dst_stride + j] (with_f2: the frame's sum(fit^2) behind its vector, at [V])
+    auto reduce_all = [&](const IterState* st, double* dst, uint64_t dst_stride, bool with_f2) -> int {
+        reduce_partials_batch_kernel<<<vgrid, 256, 0, e->stream>>>(e->d_ppart, e->gp_bp_slabs, ld, V, part_stride, dst, dst_stride, st,
+                                                                    with_f2 ? e->d_pf2part : nullptr, e->gp_fp_grid, e->gp_fp_grid);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+        return SART_OK;
+    };
+    auto back_project = [&](const IterState* st) -> int {  // d_pw -> d_psred[f], reduced over the row shards
+        SART_TRY(launch_bp(st));
+        SART_TRY(reduce_all(st, e->d_psred, V + 2, false));
+        return allreduce_f64(e, e->d_psred, (uint64_t)nf * (V + 2), ncclSum);  // all frames at once
     };
 
     // per frame: statistics, normalisation, weights of the default initial guess; one pass back-projects all of them
@@ -1204,34 +1213,76 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         CUDA_TRY(cudaGetLastError());
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;
-        if (e->cfg.nranks > 1) {  // sum(fit^2) of every frame over the row shards before the decisions
-            for (int f = 0; f < nf; ++f) {
-                f2_sum_kernel<<<1, 32, 0, e->stream>>>(e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, e->d_pf2sum + f, st_in + f);
-                CUDA_TRY(cudaGetLastError());
-                ++e->launches;
-            }
-            SART_TRY(allreduce_f64(e, e->d_pf2sum, (uint64_t)nf, ncclSum));
-            for (int f = 0; f < nf; ++f) SART_TRY(launch_decide(e, t, e->d_pf2sum + f, 1, st_in + f, st_out + f, e->d_pfs + f));
-        } else {
-            for (int f = 0; f < nf; ++f)
-                SART_TRY(launch_decide(e, t, e->d_pf2part + (uint64_t)f * e->gp_fp_grid, e->gp_fp_grid, st_in + f, st_out + f, e->d_pfs + f));
-        }
-        if (t >= e->cfg.max_iterations) return SART_OK;
-        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
-        SART_TRY(back_project(st_out));
-        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
-        for (int f = 0; f < nf; ++f) {
-            UpdArgs u = make_update_args(e, t, st_out + f);
-            u.sred = e->d_psred + f * (V + 2);
-            u.xd_cur = e->d_pxd[t & 1] + f * V;
-            u.xd_next = e->d_pxd[(t + 1) & 1] + f * V;
-            u.xf_next = e->d_pxf[(t + 1) & 1] + f * ld;
-            u.fs = e->d_pfs + f;
-            u.obs = e->d_pobs + f * V;
-            update_kernel<<<vblocks, 256, 0, e->stream>>>(u);
+        const bool last = t >= e->cfg.max_iterations;
+        UpdArgs u = make_update_args(e, t, st_out);  // base pointers: the kernels step to their frame
+        u.sred = e->d_psred;
+        u.xd_cur = e->d_pxd[t & 1];
+        u.xd_next = e->d_pxd[(t + 1) & 1];
+        u.xf_next = e->d_pxf[(t + 1) & 1];
+        u.fs = e->d_pfs;
+        u.obs = e->d_pobs;
+        if (multi && e->peer_exchange && !last) {
+            // back projection, then reduction over the ranks + decision + update of every frame in one kernel over peer
+            // memory (the frames' partial vectors lie one after the other in this rank's exchange buffer)
+            if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+            SART_TRY(launch_bp(st_in));
+            if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+            ++e->xchg_epoch;  // same count on every rank
+            SART_TRY(reduce_all(st_in, reinterpret_cast<double*>(e->d_xchg + e->xchg_buf_off[e->xchg_epoch & 1]), V + 1, true));
+            XchgArgs x;
+            x.peers = e->d_peers;
+            x.nranks = (uint32_t)e->cfg.nranks;
+            x.rank = (uint32_t)e->cfg.rank;
+            x.epoch = e->xchg_epoch;
+            x.buf_off = e->xchg_buf_off[e->xchg_epoch & 1];
+            x.st_in = st_in;
+            x.st_out = st_out;
+            x.tol = e->cfg.conv_tolerance;
+            x.max_iter = e->cfg.max_iterations;
+            x.fixed = e->cfg.fixed_iterations;
+            x.t = t;
+            u.st = nullptr;
+            xchg_decide_update_batch_kernel<<<vgrid, 256, 0, e->stream>>>(x, u, ld);
             CUDA_TRY(cudaGetLastError());
             ++e->launches;
+            return SART_OK;
         }
+        DecideArgs d;
+        d.f2part = e->d_pf2part;
+        d.n = e->gp_fp_grid;
+        d.fs = e->d_pfs;
+        d.st_in = st_in;
+        d.st_out = st_out;
+        d.tol = e->cfg.conv_tolerance;
+        d.max_iter = e->cfg.max_iterations;
+        d.fixed = e->cfg.fixed_iterations;
+        d.t = t;
+        uint32_t f2_stride = e->gp_fp_grid;
+        if (multi) {  // sum(fit^2) of every frame over the row shards before the decisions
+            f2_sum_batch_kernel<<<nf, 32, 0, e->stream>>>(e->d_pf2part, e->gp_fp_grid, e->gp_fp_grid, e->d_pf2sum, st_in);
+            CUDA_TRY(cudaGetLastError());
+            ++e->launches;
+            SART_TRY(allreduce_f64(e, e->d_pf2sum, (uint64_t)nf, ncclSum));
+            d.f2part = e->d_pf2sum;
+            d.n = 1;
+            f2_stride = 1;
+        }
+        decide_batch_kernel<<<nf, 32, 0, e->stream>>>(d, f2_stride);
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
+        if (last) return SART_OK;
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][2], e->stream));
+        SART_TRY(launch_bp(st_out));
+        if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][3], e->stream));
+        if (!multi) {  // slab sums and update of every frame in one launch
+            reduce_update_batch_kernel<<<vgrid, 256, 0, e->stream>>>(u, ld, e->d_ppart, e->gp_bp_slabs, part_stride);
+        } else {
+            SART_TRY(reduce_all(st_out, e->d_psred, V + 2, false));
+            SART_TRY(allreduce_f64(e, e->d_psred, (uint64_t)nf * (V + 2), ncclSum));
+            update_batch_kernel<<<vgrid, 256, 0, e->stream>>>(u, ld);
+        }
+        CUDA_TRY(cudaGetLastError());
+        ++e->launches;
         return SART_OK;
     };
 
@@ -1397,7 +1448,8 @@ int setup_peer_exchange(sart_engine* e) {
     const uint64_t cta_flags_bytes = ceil_div((uint64_t)e->cfg.nranks * kLayoutCtas * 8, 256) * 256;
     const uint64_t stat_slots_bytes = ceil_div((uint64_t)kStatSlots * sizeof(StatPair), 256) * 256;
     const uint64_t flags_bytes = rank_flags_bytes + cta_flags_bytes + rank_flags_bytes + 2 * stat_slots_bytes;
-    const uint64_t buf_bytes = ceil_div((e->V + 2 * kLayoutCtas + 2) * sizeof(double), 256) * 256;
+    // ... or, in sart_solve_batch, the vectors of the frames of a group one after the other
+    const uint64_t buf_bytes = ceil_div(std::max<uint64_t>(e->V + 2 * kLayoutCtas + 2, (uint64_t)kGroup * (e->V + 1)) * sizeof(double), 256) * 256;
     e->xchg_cta_flag_off = rank_flags_bytes;
     e->xchg_stat_flag_off = rank_flags_bytes + cta_flags_bytes;
     e->xchg_stat_slot_off[0] = e->xchg_stat_flag_off + rank_flags_bytes;
@@ -2136,7 +2188,7 @@ int sart_solve_batch(sart_engine* e, int32_t nframes, const double* measurements
             e->stats.status = fin[nf - 1].status;
             e->stats.iterations = fin[nf - 1].iterations;
             e->stats.sweep_mode = SART_SWEEP_SPLIT;
-            e->stats.exchange_mode = e->cfg.nranks > 1 ? SART_EXCHANGE_NCCL : SART_EXCHANGE_NONE;
+            e->stats.exchange_mode = e->cfg.nranks <= 1 ? SART_EXCHANGE_NONE : (e->peer_exchange ? SART_EXCHANGE_PEER : SART_EXCHANGE_NCCL);
             f += nf;
         } else {
             int32_t st = 0, it = 0;

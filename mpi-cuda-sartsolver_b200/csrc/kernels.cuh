@@ -622,6 +622,29 @@ __global__ void reduce_partials_kernel(const float* __restrict__ part, uint32_t 
     sred[j] = s;
 }
 
+// The same for the frames of a group (blockIdx.y = frame): partials part_stride apart, sums sred_stride apart, the frames'
+// sum(fit^2) partials f2_stride apart. One launch instead of one per frame.
+__global__ void reduce_partials_batch_kernel(const float* __restrict__ part, uint32_t nslabs, uint64_t ld, uint64_t V,
+                                             uint64_t part_stride, double* __restrict__ sred, uint64_t sred_stride,
+                                             const IterState* st, const double* __restrict__ f2part = nullptr, uint32_t nf2 = 0,
+                                             uint32_t f2_stride = 0) {
+    const uint32_t fr = blockIdx.y;
+    if (st && st[fr].done) return;
+    part += (uint64_t)fr * part_stride;
+    sred += (uint64_t)fr * sred_stride;
+    if (f2part && blockIdx.x == 0 && threadIdx.x < 32) {
+        double f = 0.0;
+        for (uint32_t k = threadIdx.x; k < nf2; k += 32) f += f2part[(uint64_t)fr * f2_stride + k];
+        f = warp_sum(f);
+        if (threadIdx.x == 0) sred[V] = f;
+    }
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= V) return;
+    double s = 0.0;
+    for (uint32_t k = 0; k < nslabs; ++k) s += (double)part[(uint64_t)k * ld + j];
+    sred[j] = s;
+}
+
 // sum(fit^2) of this shard from the forward projection's per-CTA partials (one warp, fixed order); only launched
 // when several ranks have to all-reduce the scalar before the decision.
 __global__ void f2_sum_kernel(const double* __restrict__ f2part, uint32_t n, double* __restrict__ out, const IterState* st) {
@@ -630,6 +653,17 @@ __global__ void f2_sum_kernel(const double* __restrict__ f2part, uint32_t n, dou
     for (uint32_t k = threadIdx.x; k < n; k += 32) f += f2part[k];
     f = warp_sum(f);
     if (threadIdx.x == 0) *out = f;
+}
+
+// ... of every frame of a group: CTA f sums frame f's partials (stride apart) into out[f]
+__global__ void f2_sum_batch_kernel(const double* __restrict__ f2part, uint32_t n, uint32_t stride, double* __restrict__ out,
+                                    const IterState* st) {
+    const uint32_t fr = blockIdx.x;
+    if (st && st[fr].done) return;
+    double f = 0.0;
+    for (uint32_t k = threadIdx.x; k < n; k += 32) f += f2part[(uint64_t)fr * stride + k];
+    f = warp_sum(f);
+    if (threadIdx.x == 0) out[fr] = f;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -648,7 +682,7 @@ struct DecideArgs {
     int max_iter, fixed, t;
 };
 
-__global__ void decide_kernel(const DecideArgs a) {
+__device__ __forceinline__ void decide_body(const DecideArgs& a) {
     const IterState s = *a.st_in;
     if (s.done) {
         if (threadIdx.x == 0) *a.st_out = s;
@@ -682,6 +716,18 @@ __global__ void decide_kernel(const DecideArgs a) {
         o.k = a.t + 1;
     }
     *a.st_out = o;
+}
+
+__global__ void decide_kernel(const DecideArgs a) { decide_body(a); }
+
+// the frames of a group (sart_solve_batch) in one launch: CTA f decides frame f; f2_stride apart lie the frames' partials
+__global__ void decide_batch_kernel(DecideArgs a, uint32_t f2_stride) {
+    const uint32_t f = blockIdx.x;
+    a.f2part += (uint64_t)f * f2_stride;
+    a.fs += f;
+    a.st_in += f;
+    a.st_out += f;
+    decide_body(a);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -776,6 +822,42 @@ __global__ void update_kernel(const UpdArgs a) {
     apply_update(a, j, a.sred[j]);
 }
 
+// Frame f of a group: the frames' vectors lie one after the other ([V + 2] reduced sums, [V] iterates and obs, [ld] fp32
+// copies), their scalars and control blocks in arrays.
+__device__ __forceinline__ UpdArgs frame_view(UpdArgs u, uint32_t f, uint64_t ld) {
+    u.sred += (uint64_t)f * (u.V + 2);
+    u.xd_cur += (uint64_t)f * u.V;
+    u.xd_next += (uint64_t)f * u.V;
+    u.xf_next += (uint64_t)f * ld;
+    u.obs += (uint64_t)f * u.V;
+    u.fs += f;
+    if (u.st) u.st += f;
+    return u;
+}
+
+// update of every frame of a group in one launch (blockIdx.y = frame); sums already reduced over slabs and ranks
+__global__ void update_batch_kernel(const UpdArgs a, uint64_t ld) {
+    const UpdArgs u = frame_view(a, blockIdx.y, ld);
+    if (u.st->done) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= u.V) return;
+    apply_update(u, j, u.sred[j]);
+}
+
+// one rank: the slab partials of the back projection summed (the order of reduce_partials_kernel) and the update applied
+// in the same launch, for every frame of the group
+__global__ void reduce_update_batch_kernel(const UpdArgs a, uint64_t ld, const float* __restrict__ part, uint32_t nslabs,
+                                           uint64_t part_stride) {
+    const UpdArgs u = frame_view(a, blockIdx.y, ld);
+    if (u.st->done) return;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= u.V) return;
+    part += (uint64_t)blockIdx.y * part_stride;
+    double s = 0.0;
+    for (uint32_t k = 0; k < nslabs; ++k) s += (double)part[(uint64_t)k * ld + j];
+    apply_update(u, j, s);
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // Cross-GPU reduction + decision + update in ONE kernel over NVLink peer memory (replaces the D2H -> MPI_Allreduce ->
 // H2D round trip of the reference, sartsolver_cuda.cpp:242-244 and :253-255, and this engine's own
@@ -807,7 +889,7 @@ struct XchgArgs {
     int max_iter, fixed, t;
 };
 
-__global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs x, const UpdArgs u) {
+__device__ __forceinline__ void xchg_decide_update_body(const XchgArgs& x, const UpdArgs& u) {
     const IterState s = *x.st_in;
     const bool writer = (blockIdx.x == 0 && threadIdx.x == 0);
     if (s.done) {
@@ -877,6 +959,19 @@ __global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs 
     for (int r = 0; r < kMaxPeers; ++r)
         if (r < (int)x.nranks) sj += part[r];
     apply_update(u, j, sj);
+}
+
+__global__ void __launch_bounds__(256) xchg_decide_update_kernel(const XchgArgs x, const UpdArgs u) { xchg_decide_update_body(x, u); }
+
+// The frames of a group (blockIdx.y = frame): frame f's partial vector and sum(fit^2) lie at buffer + f (V + 1) doubles.
+// One flag round trip serves all frames: CTA (0, f) of every frame still running publishes the epoch (the same value,
+// so the repeats are harmless), and because the ranks take identical decisions the same frames run on every rank.
+__global__ void __launch_bounds__(256) xchg_decide_update_batch_kernel(XchgArgs x, const UpdArgs u, uint64_t ld) {
+    const uint32_t f = blockIdx.y;
+    x.st_in += f;
+    x.st_out += f;
+    x.buf_off += (uint64_t)f * (u.V + 1) * sizeof(double);
+    xchg_decide_update_body(x, frame_view(u, f, ld));
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

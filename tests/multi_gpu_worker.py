@@ -69,11 +69,12 @@ def main():
         # independent frames through sart_solve_batch (one matrix pass serves all, per-frame sums all-reduced together)
         frames = np.stack([(1.0 + 0.5 * k) * g[off:off + n] for k in range(5)])
         xb, stb, itb = eng.solve_batch(frames)
+        batch_exchange = eng.stats().exchange_mode
         singles = [eng.solve(f) for f in frames]
         batch = {"x": max(rel_l2(xb[k], singles[k][0]) for k in range(5)),
                  "same_status": bool(all(int(stb[k]) == singles[k][1] for k in range(5))),
                  "iteration_gap": int(max(abs(int(itb[k]) - singles[k][2]) for k in range(5))),
-                 "hash": float(np.sum(xb[4] * np.arange(1, V + 1)))}
+                 "hash": float(np.sum(xb[4] * np.arange(1, V + 1))), "exchange": int(batch_exchange)}
         # warm-started series through sart_solve_series (look-ahead) against solve-by-solve on the same ranks
         series = None
         if not kw.get("logarithmic"):

@@ -47,6 +47,8 @@ def test_sharded_solve_matches_oracle(world):
             if c["batch"] is not None:  # sart_solve_batch against frame-by-frame solves on the same ranks
                 b = c["batch"]
                 assert b["iteration_gap"] <= 1, (name, b)
+                import os as _os2  # the group's reduction travels over peer memory too, unless NCCL was asked for
+                assert b["exchange"] == (1 if _os2.environ.get("SART_EXCHANGE") == "nccl" else 2), (name, b)
                 if b["iteration_gap"] == 0:
                     assert b["same_status"] and b["x"] <= 1e-5, (name, b)
             if c["series"] is not None:  # sart_solve_series against warm-started solves on the same ranks
