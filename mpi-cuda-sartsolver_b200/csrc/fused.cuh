@@ -229,6 +229,19 @@ __device__ __forceinline__ bool grid_barrier(unsigned long long* ctr, const unsi
     return *s_abort == 0;
 }
 
+// What one sweep of a launch leaves for the next one, and what the tails decide about the sweeps to come. It lives in shared
+// memory: as registers these ~20 values would stay occupied through the row loop, where the kernel sits at its 128-register
+// cap, and the compiler then re-materialises loop invariants (thread and cluster ids, kernel parameters) inside that loop --
+// 7 % more instructions per row, which wide rows (fewer SMs streaming) feel one to one. Written by one thread of the role
+// that owns a field, read by everybody behind a CTA-wide barrier.
+struct SweepCarry {
+    double conv_prev;
+    int t, t_spec, pflip, t_first, repeated, ahead_prev;
+    uint32_t pr_stage, pr_slot, pr_parity;                                  // producer's ring / slot position
+    uint32_t rd_slot, rd_parity;                                            // reducer's
+    uint32_t fp_stage, fp_parity, fp_slot, fin_stage, fin_slot, fin_parity;  // consumers'
+};
+
 // warps 0..NWC-1 consumers, warp NWC TMA producer, warp NWC+1 reducer: 16 warps in all, so that every SM sub-partition
 // holds 4 and a thread may use 128 registers (a 17th warp caps the kernel at 96 and spills).
 // D = software-pipeline depth of the consumers: FP runs D rows ahead of FIN, so the exchange latency of a row (reducer
@@ -251,12 +264,13 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     // tail; everybody reads them behind it), and the series block as the launch found it.
     __shared__ unsigned long long s_bar_target, s_tails, s_epoch0;
     __shared__ SeriesCtl s_ctl;
+    __shared__ SweepCarry s_c;
 
-    double conv_prev = 0.0;
+    double conv_prev0 = 0.0;
     if constexpr (PERSIST) {
         const IterState s0 = *sv->st[0];
         if (s0.done) return;
-        conv_prev = s0.conv_prev;
+        conv_prev0 = s0.conv_prev;
     } else if (a.st && a.st->done) {
         return;
     }
@@ -265,8 +279,11 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     const uint32_t cid = cluster_id_x(), ncl = cluster_count_x();
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    const uint32_t ring_u32 = smem_u32(smem);
-    const uint32_t wpart_u32 = ring_u32 + S * a.stage_bytes;         // [2S][NWC] floats
+    // The two bases every row needs go through an asm statement: the compiler may then not re-derive them inside the row
+    // loop (S2R CgaCtaId + parameter loads + multiply, several times per row) when registers are tight; it keeps them.
+    uint32_t ring_u32, wpart_u32;
+    asm volatile("mov.u32 %0, %1;" : "=r"(ring_u32) : "r"(smem_u32(smem)));
+    asm volatile("mov.u32 %0, %1;" : "=r"(wpart_u32) : "r"(ring_u32 + S * a.stage_bytes));  // [2S][NWC] floats
     const uint32_t cdot_u32 = wpart_u32 + 2 * S * NWC * 4;       // [2S][CSTRIDE] floats
     const uint32_t full_u32 = cdot_u32 + 2 * S * CSTRIDE * 4;
     const uint32_t empty_u32 = full_u32 + 8 * S, wbar_u32 = empty_u32 + 8 * S, dot_u32 = wbar_u32 + 16 * S;
@@ -293,6 +310,24 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             }
             s_ctl = c;
         }
+        {
+            SweepCarry k = {};
+            k.conv_prev = conv_prev0;
+            k.t_spec = -1;
+            k.pr_parity = 1;
+            if constexpr (PERSIST) {
+                if (sv->series) {
+                    if (s_ctl.handed) {
+                        k.t_first = 1;
+                        k.pflip = s_ctl.pflip;
+                    }
+                    const int d = s_ctl.it_prev - s_ctl.it_prev2;
+                    if (sv->has_next && s_ctl.it_prev >= 2 && s_ctl.it_prev2 >= 2 && d >= -2 && d <= 2) k.t_spec = s_ctl.it_prev;
+                }
+            }
+            k.t = k.t_first;
+            s_c = k;
+        }
         for (uint32_t s = 0; s < S; ++s) {
             mbar_init(full_u32 + 8 * s, 1);
             mbar_init(empty_u32 + 8 * s, NWC);
@@ -306,45 +341,23 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
     cluster_sync_all();
 
     const uint32_t n = (a.P > cid) ? (uint32_t)((a.P - cid + ncl - 1) / ncl) : 0;
-    // ring / slot positions of the three roles; they run on from sweep to sweep
-    uint32_t pr_stage = 0, pr_slot = 0, pr_parity = 1;                                    // producer
-    uint32_t rd_slot = 0, rd_parity = 0;                                                  // reducer
-    uint32_t fp_stage = 0, fp_parity = 0, fp_slot = 0, fin_stage = 0, fin_slot = 0, fin_parity = 0;  // consumers
-
-    int t_spec = -1, pflip = 0, t_first = 0;
-    bool repeated = false;
-    if constexpr (PERSIST) {
-        if (sv->series) {  // (s_ctl: written before the cluster-wide synchronisation above)
-            if (s_ctl.handed) {
-                t_first = 1;
-                pflip = s_ctl.pflip;
-            }
-            const int d = s_ctl.it_prev - s_ctl.it_prev2;
-            if (sv->has_next && s_ctl.it_prev >= 2 && s_ctl.it_prev2 >= 2 && d >= -2 && d <= 2) t_spec = s_ctl.it_prev;
-        }
-    }
-    // Rows of the coming sweep whose copies the producer already issued while the previous tail was running: the matrix
-    // does not depend on the iterate, so the producer simply keeps going into the next sweep's first rows as the
-    // consumers release the last stages of this one, and the reduction / exchange / update between two sweeps overlaps
-    // with refilling the whole shared-memory ring (S row panels per SM) from HBM. Same on every thread (uniform inputs).
-    bool ahead_prev = false;  // the previous tail of this launch was overlapped that way
-    for (int t = t_first;; ++t) {
-        const float* xcur = a.x;
-        const float* gsrc = a.g;
-        if constexpr (PERSIST) {
-            xcur = sv->xf[(t + pflip) & 1];
-            if (t == t_spec) gsrc = sv->g_spec;
-        }
-        // another sweep can only follow while t < max_iter (the decision of sweep max_iter is always "stop"), and none
-        // is expected after the sweep a series predicts to be the frame's last
-        auto runs_ahead = [&]() {
-            if constexpr (PERSIST) return sv->prefetch && t < sv->max_iter && t != t_spec;
-            else return false;
-        };
-
+    // The ring / slot positions of the three roles run on from sweep to sweep (s_c, each role loads its own at the start of
+    // a sweep and stores them at the end). s_c.ahead_prev: rows of the coming sweep whose copies the producer already issued
+    // while the previous tail was running -- the matrix does not depend on the iterate, so the producer simply keeps going
+    // into the next sweep's first rows as the consumers release the last stages of this one, and the reduction / exchange /
+    // update between two sweeps overlaps with refilling the whole shared-memory ring (S row panels per SM) from HBM.
+    // Another sweep can only follow while t < max_iter (the decision of sweep max_iter is always "stop"), and none is
+    // expected after the sweep a series predicts to be the frame's last.
+    auto runs_ahead = [&](int t, int t_spec) {
+        if constexpr (PERSIST) return sv->prefetch && t < sv->max_iter && t != t_spec;
+        else return false;
+    };
+    for (;;) {
         if (warp == NWC) {
             // ---- producer --------------------------------------------------------------------------------------------
             if (lane == 0) {
+                uint32_t pr_stage = s_c.pr_stage, pr_slot = s_c.pr_slot, pr_parity = s_c.pr_parity;
+                const bool ahead_prev = s_c.ahead_prev != 0;
                 const uint32_t bytes = wcols * 16;
                 const char* src0 = reinterpret_cast<const char*>(a.H) + ((uint64_t)cid * a.ld4 + c0) * 16;
                 const uint64_t src_step = (uint64_t)ncl * a.ld4 * 16;
@@ -363,10 +376,13 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 const char* src = src0 + (uint64_t)pre * src_step;
                 for (uint32_t r = pre; r < n; ++r, src += src_step) issue(src);
                 if constexpr (PERSIST) {
-                    const uint32_t npre = runs_ahead() ? min(S, n) : 0u;
+                    const uint32_t npre = runs_ahead(s_c.t, s_c.t_spec) ? min(S, n) : 0u;
                     src = src0;
                     for (uint32_t r = 0; r < npre; ++r, src += src_step) issue(src);  // the next sweep's first rows
                 }
+                s_c.pr_stage = pr_stage;
+                s_c.pr_slot = pr_slot;
+                s_c.pr_parity = pr_parity;
             }
             __syncwarp();
         } else if (warp == NWC + 1) {
@@ -374,6 +390,7 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             const uint32_t peer = (lane < C) ? lane : 0;
             const uint32_t peer_cdot0 = map_to_cta(cdot_u32 + rank * 4, peer);
             const uint32_t peer_dot0 = map_to_cta(dot_u32, peer);
+            uint32_t rd_slot = s_c.rd_slot, rd_parity = s_c.rd_parity;
             for (uint32_t r = 0; r < n; ++r) {
                 mbar_wait(wbar_u32 + 8 * rd_slot, rd_parity);
                 float p = (lane < NWC) ? lds32(wpart_u32 + (rd_slot * NWC + lane) * 4) : 0.f;
@@ -385,8 +402,21 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 }
             }
             __syncwarp();
+            if (lane == 0) {
+                s_c.rd_slot = rd_slot;
+                s_c.rd_parity = rd_parity;
+            }
         } else {
             // ---- consumers -------------------------------------------------------------------------------------------
+            const float* xcur = a.x;
+            const float* gsrc = a.g;
+            if constexpr (PERSIST) {
+                const int t = s_c.t;
+                xcur = sv->xf[(t + s_c.pflip) & 1];
+                if (t == s_c.t_spec) gsrc = sv->g_spec;
+            }
+            uint32_t fp_stage = s_c.fp_stage, fp_parity = s_c.fp_parity, fp_slot = s_c.fp_slot;
+            uint32_t fin_stage = s_c.fin_stage, fin_slot = s_c.fin_slot, fin_parity = s_c.fin_parity;
             const int mine = (wcols > tid) ? (int)((wcols - tid + NT - 1) / NT) : 0;
             float4 xr[K], sacc[K];
             const float4* x4 = reinterpret_cast<const float4*>(xcur) + c0 + tid;
@@ -501,6 +531,14 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             for (int m = 0; m < K; ++m)
                 if (m < mine) out4[m * NT] = sacc[m];
             if (rank == 0 && tid == 0) a.f2part[cid] = f2acc;
+            if (tid == 0) {  // (every consumer thread holds the same positions)
+                s_c.fp_stage = fp_stage;
+                s_c.fp_parity = fp_parity;
+                s_c.fp_slot = fp_slot;
+                s_c.fin_stage = fin_stage;
+                s_c.fin_slot = fin_slot;
+                s_c.fin_parity = fin_parity;
+            }
         }
         if constexpr (!PERSIST) {
             break;
@@ -523,6 +561,11 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             bool ok = grid_barrier(sv->gbar, &s_bar_target, &s_abort);
             if (timer) sv->tail_ns[2] = global_timer_ns();  // the slowest cluster has finished its rows
             phase_done(0);
+            // the carry as the sweep left it; thread 0 rewrites it at the end of the tail, behind the __syncthreads below
+            const int t = s_c.t, pflip = s_c.pflip, t_first = s_c.t_first;
+            int t_spec = s_c.t_spec;
+            bool repeated = s_c.repeated != 0;
+            double conv_prev = s_c.conv_prev;
             const uint64_t V = sv->V, chunk = (V + nblk - 1) / nblk;
             const uint64_t j0 = min(V, (uint64_t)blk * chunk), j1 = min(V, j0 + chunk);
             // this rank's partial of voxel j: the clusters' partials in fixed order (reduce_partials_kernel)
@@ -640,8 +683,8 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             // CTA may exit (its shared memory is their destination).
             auto drain = [&]() {
                 if (tid == 0) {
-                    uint32_t st = fp_stage, par = fp_parity;
-                    const uint32_t npre = runs_ahead() ? min(S, n) : 0u;
+                    uint32_t st = s_c.fp_stage, par = s_c.fp_parity;  // (thread 0 stored them itself)
+                    const uint32_t npre = runs_ahead(t, t_spec) ? min(S, n) : 0u;
                     for (uint32_t i = 0; i < npre; ++i) {
                         mbar_wait(full_u32 + 8 * st, par);
                         if (++st == S) {
@@ -694,7 +737,16 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
                 drain();
                 break;
             }
-            if (tid == 0) s_bar_target += nblk;
+            if (tid == 0) {
+                s_bar_target += nblk;
+                // the next sweep: t + 1, or -- after a wrong prediction, once the partials of this sweep have been read by
+                // everyone (barrier below) -- sweep t again with this frame's own measurement
+                s_c.ahead_prev = runs_ahead(t, t_spec) ? 1 : 0;
+                s_c.conv_prev = conv_prev;
+                s_c.t = redo ? t : t + 1;
+                s_c.t_spec = redo ? -1 : t_spec;
+                s_c.repeated = redo ? 1 : (repeated ? 1 : 0);
+            }
             if (!grid_barrier(sv->gbar, &s_bar_target, &s_abort)) {
                 drain();
                 if (tid == 0) {
@@ -720,12 +772,6 @@ __device__ __forceinline__ void fused_body(const FusedArgs& a, const SolveArgs* 
             if (timer) {
                 sv->tail_ns[0] += global_timer_ns() - sv->tail_ns[2];
                 sv->tail_ns[1] += 1;
-            }
-            ahead_prev = runs_ahead();
-            if (redo) {  // the partials of this sweep have been read by everyone (barrier above): run sweep t again
-                t_spec = -1;
-                repeated = true;
-                --t;
             }
         }
     }

@@ -1,9 +1,9 @@
 #!/usr/bin/env python
-"""Prints the few numbers of a bench.py JSON line that matter when comparing runs."""
+"""Prints the few numbers of a bench.py JSON line that matter when comparing runs: bench_brief.py FILE... (or on stdin)."""
+import fileinput
 import json
-import sys
 
-for line in sys.stdin:
+for line in fileinput.input():
     if not line.startswith("{"):
         if line.strip():
             print(line.rstrip()[:300])
