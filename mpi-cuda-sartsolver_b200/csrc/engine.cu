@@ -24,6 +24,7 @@
 #include "../../include/sart_b200.h"
 #include "kernels.cuh"
 #include "fused.cuh"
+#include "batch_ring.cuh"
 #include "nccl_dyn.h"
 
 using namespace sart;
@@ -176,6 +177,10 @@ struct sart_engine {
     bool group_planned = false, group_ok = false;
     uint32_t gp_fp_grid = 0, gp_bp_slabs = 0, gp_bp_rows_per_slab = 0;
     int group_frames = 8, gp_fp_rows = 8, gp_fp_threads = 384;  // frames per matrix pass; rows per thread / threads per CTA of the batched forward kernel
+    uint32_t gp_fp_ring_stages = 0, gp_fp_ring_smem = 0;         // > 0: the shared-memory-ring forward kernel (batch_ring.cuh) runs
+    CUtensorMap gp_map_h, gp_map_x[2];                           // its tensor maps: the shard, the two buffers of the group's iterates
+    uint32_t gp_bp_ring_stages = 0, gp_bp_ring_smem = 0;         // > 0: the ring back-projection kernel runs
+    CUtensorMap gp_map_h_bp;                                     // the shard in boxes of kBpRingRows rows
     double *d_pgd = nullptr, *d_pxio = nullptr, *d_psred = nullptr, *d_pf2part = nullptr, *d_pf2sum = nullptr, *d_pobs = nullptr;
     double* d_pxd[2] = {nullptr, nullptr};   // [parity] -> [kGroup][V]
     float* d_pxf[2] = {nullptr, nullptr};    // [parity] -> [kGroup][ld]
@@ -1051,6 +1056,34 @@ int run_solve(sart_engine* e, int has_guess) {
 // SART_BATCH_FRAMES picks, buffers are sized for kGroup = the larger one.
 constexpr int kGroup = 8;
 
+// Tensor map of a row-major fp32 array [rows][ld] for boxes of [box_rows][kRingCols4 * 4 columns] (batch_ring.cuh). The
+// encoder is a driver function; it is looked up through the runtime, so the library still does not link libcuda.
+bool encode_rows_map(CUtensorMap* map, const float* base, uint64_t rows, uint64_t ld, uint32_t box_rows) {
+    using EncodeTiled = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                     const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeTiled encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult found = cudaDriverEntryPointSymbolNotFound;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &found) != cudaSuccess ||
+            found != cudaDriverEntryPointSuccess)
+            fn = nullptr;
+        (void)cudaGetLastError();
+        return reinterpret_cast<EncodeTiled>(fn);
+    }();
+    if (!encode || (reinterpret_cast<uintptr_t>(base) & 15) || (ld * sizeof(float)) % 16 || ld >= (1ull << 32) || rows >= (1ull << 32))
+        return false;
+    const cuuint64_t dims[2] = {ld, rows};
+    const cuuint64_t strides[1] = {ld * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)(kRingCols4 * 4), box_rows};
+    const cuuint32_t steps[2] = {1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, steps,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+constexpr const char* kBatchFpDefault = "ring";
+constexpr const char* kBatchBpDefault = "ring";  // back projection of eight-frame groups: "ring" or "smem" (kernels.cuh)  // forward kernel of eight-frame groups: "ring" (batch_ring.cuh) or "warp"
 constexpr int kFp8Threads = 384, kFp8Rows = 8;  // eight frames: 8 rows x 8 frames of accumulators per thread, one CTA per SM
 template <int F>
 struct GroupKernels {
@@ -1086,12 +1119,55 @@ int plan_group(sart_engine* e) {
     const uint64_t nrg = ceil_div(e->P, (uint64_t)e->gp_fp_rows);
     const uint64_t groups_per_cta = e->group_frames == 8 ? kFp8Threads / 32 : 1;
     e->gp_fp_grid = (uint32_t)std::min<uint64_t>(ceil_div(nrg, groups_per_cta), (uint64_t)e->sm_count * std::max(fp_occ, 1));
+    // eight frames: the forward kernel that stages the matrix through a shared-memory ring (SART_BATCH_FP=warp keeps the
+    // register-file one), when the device grants the shared memory for at least two stages
+    e->gp_fp_ring_stages = 0;
+    const uint32_t warp_grid = e->gp_fp_grid;
+    const int warp_rows = e->gp_fp_rows, warp_threads = e->gp_fp_threads;
+    const char* fp_kind = std::getenv("SART_BATCH_FP");
+    if (e->group_frames == 8 && std::string(fp_kind ? fp_kind : kBatchFpDefault) == "ring") {
+        int max_smem = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+        const uint32_t stages = ring_stages<8>(max_smem);
+        if (stages >= 2 &&
+            cudaFuncSetAttribute(fp_rows_batch_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)ring_smem_bytes<8>(stages)) == cudaSuccess) {
+            e->gp_fp_ring_stages = stages;
+            e->gp_fp_ring_smem = ring_smem_bytes<8>(stages);
+            e->gp_fp_rows = kRingRows;
+            e->gp_fp_threads = kRingThreads;
+            e->gp_fp_grid = (uint32_t)std::min<uint64_t>(ceil_div(e->P, (uint64_t)kRingRows), (uint64_t)e->sm_count);
+        }
+        (void)cudaGetLastError();
+    }
     // back projection: one wave of (panels x slabs) CTAs at this kernel's own occupancy, slabs a multiple of 32 rows
     const uint64_t panels = ceil_div(e->ld4, kBpThreads);
     uint64_t slabs = std::max<uint64_t>(1, (uint64_t)e->sm_count * std::max(bp_occ, 1) / panels);
     slabs = std::min<uint64_t>(slabs, ceil_div(e->P, 32));
     e->gp_bp_rows_per_slab = (uint32_t)(ceil_div(ceil_div(e->P, slabs), 32) * 32);
     e->gp_bp_slabs = (uint32_t)ceil_div(e->P, e->gp_bp_rows_per_slab);
+
+    // the same for the back projection (SART_BATCH_BP): panels of 256 columns x slabs of rows, about four waves of CTAs
+    e->gp_bp_ring_stages = 0;
+    const uint32_t smem_slabs = e->gp_bp_slabs, smem_rows_per_slab = e->gp_bp_rows_per_slab;
+    const char* bp_kind = std::getenv("SART_BATCH_BP");
+    if (e->group_frames == 8 && std::string(bp_kind ? bp_kind : kBatchBpDefault) == "ring") {
+        int max_smem = 0;
+        CUDA_TRY(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, e->device));
+        const uint32_t stages = bp_ring_stages<8>(max_smem);
+        if (stages >= 2 &&
+            cudaFuncSetAttribute(bp_cols_batch_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)bp_ring_smem_bytes<8>(stages)) == cudaSuccess) {
+            const uint64_t ring_panels = ceil_div(e->ld4, (uint64_t)kBpRingCols4);
+            uint64_t ring_slabs = std::max<uint64_t>(1, (uint64_t)e->sm_count * 4 / ring_panels);
+            ring_slabs = std::min<uint64_t>(ring_slabs, ceil_div(e->P, (uint64_t)kBpRingRows));
+            e->gp_bp_rows_per_slab = (uint32_t)(ceil_div(ceil_div(e->P, ring_slabs), (uint64_t)kBpRingRows) * kBpRingRows);
+            e->gp_bp_slabs = (uint32_t)ceil_div(e->P, e->gp_bp_rows_per_slab);
+            e->gp_bp_ring_stages = stages;
+            e->gp_bp_ring_smem = bp_ring_smem_bytes<8>(stages);
+        }
+        (void)cudaGetLastError();
+    }
 
     const uint64_t G = kGroup;
     SART_TRY(dev_alloc(&e->d_pgd, G * e->P));
@@ -1100,9 +1176,9 @@ int plan_group(sart_engine* e) {
     SART_TRY(dev_alloc(&e->d_pxio, G * e->V));
     SART_TRY(dev_alloc(&e->d_pobs, G * e->V));
     SART_TRY(dev_alloc(&e->d_psred, G * (e->V + 2)));
-    SART_TRY(dev_alloc(&e->d_pf2part, G * (uint64_t)e->gp_fp_grid));
+    SART_TRY(dev_alloc(&e->d_pf2part, G * (uint64_t)std::max(e->gp_fp_grid, warp_grid)));
     SART_TRY(dev_alloc(&e->d_pf2sum, G));
-    SART_TRY(dev_alloc(&e->d_ppart, G * (uint64_t)e->gp_bp_slabs * e->ld));
+    SART_TRY(dev_alloc(&e->d_ppart, G * (uint64_t)std::max(e->gp_bp_slabs, smem_slabs) * e->ld));
     SART_TRY(dev_alloc(&e->d_pfs, G));
     for (int k = 0; k < 2; ++k) {
         SART_TRY(dev_alloc(&e->d_pxd[k], G * e->V));
@@ -1110,6 +1186,19 @@ int plan_group(sart_engine* e) {
         SART_TRY(dev_alloc(&e->d_pst[k], G));
     }
     CUDA_TRY(cudaMallocHost(reinterpret_cast<void**>(&e->h_pst), 2 * G * sizeof(IterState)));
+    if (e->gp_fp_ring_stages &&
+        !(encode_rows_map(&e->gp_map_h, e->dH, e->P, e->ld, kRingRows) && encode_rows_map(&e->gp_map_x[0], e->d_pxf[0], G, e->ld, (uint32_t)G) &&
+          encode_rows_map(&e->gp_map_x[1], e->d_pxf[1], G, e->ld, (uint32_t)G))) {
+        e->gp_fp_ring_stages = 0;  // no tensor maps on this driver: the register-file kernel
+        e->gp_fp_grid = warp_grid;
+        e->gp_fp_rows = warp_rows;
+        e->gp_fp_threads = warp_threads;
+    }
+    if (e->gp_bp_ring_stages && !encode_rows_map(&e->gp_map_h_bp, e->dH, e->P, e->ld, kBpRingRows)) {
+        e->gp_bp_ring_stages = 0;
+        e->gp_bp_slabs = smem_slabs;
+        e->gp_bp_rows_per_slab = smem_rows_per_slab;
+    }
     e->group_ok = true;
     return SART_OK;
 }
@@ -1133,8 +1222,12 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         b.rows_per_slab = e->gp_bp_rows_per_slab;
         b.st = st;
         b.nframes = nf;
-        (e->group_frames == 8 ? GroupKernels<8>::bp() : GroupKernels<4>::bp())
-            <<<dim3((uint32_t)ceil_div(e->ld4, kBpThreads), e->gp_bp_slabs), kBpThreads, 0, e->stream>>>(b);
+        if (e->gp_bp_ring_stages)
+            bp_cols_batch_ring_kernel<8><<<dim3((uint32_t)ceil_div(e->ld4, (uint64_t)kBpRingCols4), e->gp_bp_slabs), kBpRingThreads,
+                                           e->gp_bp_ring_smem, e->stream>>>(b, e->gp_bp_ring_stages, e->gp_map_h_bp);
+        else
+            (e->group_frames == 8 ? GroupKernels<8>::bp() : GroupKernels<4>::bp())
+                <<<dim3((uint32_t)ceil_div(e->ld4, kBpThreads), e->gp_bp_slabs), kBpThreads, 0, e->stream>>>(b);
         CUDA_TRY(cudaGetLastError());
         ++e->launches;
         return SART_OK;
@@ -1209,7 +1302,11 @@ int run_solve_group(sart_engine* e, int nf, IterState* fin) {
         a.nframes = nf;
         a.log_mode = e->cfg.logarithmic;
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][0], e->stream));
-        (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, e->gp_fp_threads, 0, e->stream>>>(a);
+        if (e->gp_fp_ring_stages)
+            fp_rows_batch_ring_kernel<8><<<e->gp_fp_grid, kRingThreads, e->gp_fp_ring_smem, e->stream>>>(a, e->gp_fp_ring_stages, e->gp_map_h,
+                                                                                                           e->gp_map_x[t & 1]);
+        else
+            (e->group_frames == 8 ? GroupKernels<8>::fp() : GroupKernels<4>::fp())<<<e->gp_fp_grid, e->gp_fp_threads, 0, e->stream>>>(a);
         CUDA_TRY(cudaGetLastError());
         if (prof) CUDA_TRY(cudaEventRecord(e->ev_prof[t][1], e->stream));
         ++e->launches;
