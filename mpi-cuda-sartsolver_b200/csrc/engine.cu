@@ -331,7 +331,7 @@ FusedCandidate probe_fused(sart_engine* e, uint32_t C, int max_smem) {
     for (uint32_t s = s_cap; s >= 2; --s) {
         // stages + warp partials [2S][NWC] + per-CTA sums [2S][16] + barriers full[S], empty[S], wbar[2S], dot[2S]
         const uint64_t need = (uint64_t)s * c.stage_bytes + (uint64_t)2 * s * nw * 4 + (uint64_t)2 * s * 16 * 4 + (uint64_t)6 * s * 8;
-                if (need + 512 <= (uint64_t)max_smem) {  // + the kernel's static shared variables (384 bytes)
+        if (need + 512 <= (uint64_t)max_smem) {  // + the kernel's static shared variables (384 bytes)
             c.S = s;
             c.smem = (uint32_t)need;
             break;
