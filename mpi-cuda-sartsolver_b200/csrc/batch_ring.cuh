@@ -26,10 +26,10 @@
 
 namespace sart {
 
-constexpr int kRingRowsPerGroup = 8, kRingRowGroups = 4, kRingQuarters = 2;
+constexpr int kRingRowsPerGroup = 8, kRingRowGroups = 4, kRingHalves = 2;
 constexpr int kRingRows = kRingRowsPerGroup * kRingRowGroups;            // rows of a stage
-constexpr int kRingCols4 = 32 * kRingQuarters;                           // float4 columns of a stage
-constexpr int kRingConsumerWarps = kRingRowGroups * kRingQuarters;       // 8
+constexpr int kRingCols4 = 32 * kRingHalves;                           // float4 columns of a stage
+constexpr int kRingConsumerWarps = kRingRowGroups * kRingHalves;       // 8
 constexpr int kRingThreads = 32 * (kRingConsumerWarps + 1);              // + the producer warp
 constexpr int kRingRowBytes = kRingCols4 * 16;                           // 1 KB of a row (or of a frame's x) per stage
 static_assert(kRingRows <= 256 && kRingCols4 * 4 <= 256, "a box of a tensor map has at most 256 elements per dimension");
@@ -45,10 +45,10 @@ template <int F>
 __host__ __device__ constexpr uint32_t ring_stage_bytes() {
     return (uint32_t)(kRingRows + F) * kRingRowBytes;
 }
-// stages that fit: the ring, two mbarriers per stage, the static arrays of the kernel (cross-quarter sums, sum(fit^2))
+// stages that fit: the ring, two mbarriers per stage, the static arrays of the kernel (cross-half sums, sum(fit^2))
 template <int F>
 inline uint32_t ring_stages(int max_smem) {
-    const int reserve = 2 * kRingRowGroups * kRingQuarters * 64 * 8 + 1024;
+    const int reserve = 2 * kRingRowGroups * kRingHalves * 64 * 8 + 1024;
     int s = (max_smem - reserve) / (int)(ring_stage_bytes<F>() + 16);
     return (uint32_t)(s > 8 ? 8 : s);
 }
@@ -62,7 +62,7 @@ template <int F>
 __global__ void __launch_bounds__(kRingThreads, 1)
     fp_rows_batch_ring_kernel(const FpBatchArgs a, uint32_t S, const __grid_constant__ CUtensorMap map_h,
                               const __grid_constant__ CUtensorMap map_x) {
-    constexpr int R = kRingRowsPerGroup, G = kRingRowGroups, Q = kRingQuarters, NWC = kRingConsumerWarps;
+    constexpr int R = kRingRowsPerGroup, G = kRingRowGroups, Q = kRingHalves, NWC = kRingConsumerWarps;
     static_assert((R * F) % 32 == 0 && 32 % F == 0, "whole (row, frame) slots per lane in the epilogue");
     constexpr int PER_LANE = R * F / 32;
     if (a.st) {
@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         if (all_done) return;
     }
     extern __shared__ __align__(128) unsigned char ring[];
-    __shared__ double red[2][G][Q][R * F];  // a row block's sums per column quarter (two row blocks in flight)
+    __shared__ double red[2][G][Q][R * F];  // a row block's sums per column half (two row blocks in flight)
     __shared__ double f2s[G][F];
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr uint32_t stage_bytes = ring_stage_bytes<F>();
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     const int my_r = lane / F, my_f = lane % F;
     const uint32_t h_off = (g * R * kRingCols4 + q * 32 + lane) * 16;   // this lane's float4 of row 8 g in a stage
     const uint32_t x_off = (kRingRows * kRingCols4 + q * 32 + lane) * 16;  // ... of frame 0's x
-    double f2acc = 0.0;  // of frame my_f, this lane's row slots (warps of quarter 0)
+    double f2acc = 0.0;  // of frame my_f, this lane's row slots (warps of half 0)
     uint32_t nblock = 0;
     for (uint32_t rb = blockIdx.x; rb < a.nrg; rb += gridDim.x, ++nblock) {
         const uint64_t row0 = (uint64_t)rb * kRingRows + g * R;
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         double(*slot)[Q][R * F] = red[nblock & 1];
 #pragma unroll
         for (int k = 0; k < PER_LANE; ++k) slot[g][q][k * 32 + lane] = mine[k];
-        // all consumer warps: the block's quarters are complete (and the other slot of `red` is free again, see below)
+        // all consumer warps: the block's halves are complete (and the other slot of `red` is free again, see below)
         asm volatile("bar.sync 1, %0;" ::"n"(32 * NWC) : "memory");
         if (q == 0) {
 #pragma unroll
@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
                 }
             }
         }
-        // slot reuse: block n + 2 writes red[n & 1] after the barrier of block n + 1, which the quarter-0 warps only
+        // slot reuse: block n + 2 writes red[n & 1] after the barrier of block n + 1, which the half-0 warps only
         // reach once they have read block n's sums
     }
     // sum(fit^2) per frame: over the row slots of a warp (lanes f, f + F, ...), then over the row groups in order
